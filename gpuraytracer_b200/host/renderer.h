@@ -1,0 +1,44 @@
+// renderer.h -- headless C++ Renderer: same member names and call order as the reference's
+// Renderer (src/Renderer.h:15-135), with the D3D12 device, swap chain and window replaced by a
+// gprt_ctx (CUDA) and a host/device framebuffer.
+#pragma once
+#include <cstdint>
+
+#include "../../include/gprt.h"
+#include "scene.h"
+
+namespace gprt_host {
+
+class Renderer {
+public:
+    Renderer(int scene_id, uint32_t width, uint32_t height, uint32_t grid_n, int device, const gprt_config* config_override);
+    ~Renderer();
+
+    int on_init();                                               // src/Renderer.cpp:56-80
+    int on_update(float animate_geometry_time, float camera_orbit_deg, float light_orbit_deg); // :82-120
+    int on_render(gprt_rect tile, void* h_rgba8, uint32_t* h_hit_ids); // :122-148
+    int on_size_changed(uint32_t width, uint32_t height);        // :150-161
+    void on_destroy();                                           // :163-170
+
+    int do_raytracing(gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, float* d_rgba_f32); // :401-452
+    float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399
+
+    SceneState& scene() { return m_scene; }
+    gprt_ctx* context() { return m_ctx; }
+    bool valid() const { return m_valid; }
+
+private:
+    int create_device_dependent_resources();  // :987-1021
+    int build_geometry();                      // :478-565  -> gprt_set_geometry
+    int build_shader_tables();                 // :839-985  -> gprt_set_hit_group_table
+    int build_acceleration_structures();       // :788-835  -> gprt_build_accel
+
+    SceneState m_scene;
+    gprt_ctx* m_ctx = nullptr;
+    int m_device = -1;
+    bool m_valid = false;
+    bool m_initialized = false;
+    gprt_rect m_last_tile = {0, 0, 0, 0};
+};
+
+} // namespace gprt_host

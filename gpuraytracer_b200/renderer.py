@@ -1,0 +1,160 @@
+"""Python face of the headless Renderer (thin: every call goes straight to libgprt.so).
+
+Mirrors the reference's Renderer entry points (src/Renderer.h:24-28): on_init, on_update,
+on_render, on_size_changed, on_destroy, plus do_raytracing for device-resident output.
+torch is used only to hold device buffers; nothing is computed in Python.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _capi
+from ._capi import Config, Counters, Rect, SceneView, Timing, check, lib
+
+
+@dataclass
+class SceneData:
+    """Host copies of everything do_raytracing / build_acceleration_structures consume."""
+    width: int
+    height: int
+    config: Config
+    scene_cb: np.ndarray    # SCENE_CB_DTYPE, shape (1,)
+    per_frame: np.ndarray   # PER_FRAME_DTYPE, shape (n,)
+    aabbs: np.ndarray       # AABB_DTYPE, shape (n,)
+    hit_groups: np.ndarray  # HIT_GROUP_DTYPE, shape (2 + 2n,)
+    vertices: np.ndarray
+    indices: np.ndarray     # uint16
+    instances: np.ndarray   # INSTANCE_DTYPE, shape (2,)
+
+
+def default_config() -> Config:
+    cfg = Config()
+    lib().gprt_default_config(C.byref(cfg))
+    return cfg
+
+
+class Renderer:
+    """scene_id 0 = reference scene; 1..5 = BASELINE configs; 6 = config 3 with long march budget.
+
+    device=None builds the scene only (for feeding the oracle in CPU tests); rendering then
+    raises GprtError(GPRT_E_NO_DEVICE): there is no CPU render path in this package.
+    """
+
+    def __init__(self, scene_id=0, width=0, height=0, grid_n=0, device=0, config: Config = None):
+        self._h = C.c_void_p()
+        self._lib = lib()
+        dev = -1 if device is None else int(device)
+        check(self._lib.gprt_renderer_create(C.byref(self._h), int(scene_id), int(width), int(height), int(grid_n), dev,
+                                             C.byref(config) if config is not None else None), "renderer_create")
+        self.device = device
+
+    def on_init(self):
+        check(self._lib.gprt_renderer_on_init(self._h), "on_init")
+        return self
+
+    def on_update(self, animate_geometry_time=0.0, camera_orbit_deg=0.0, light_orbit_deg=0.0):
+        check(self._lib.gprt_renderer_on_update(self._h, float(animate_geometry_time), float(camera_orbit_deg), float(light_orbit_deg)),
+              "on_update")
+
+    def on_size_changed(self, width, height):
+        check(self._lib.gprt_renderer_on_size_changed(self._h, int(width), int(height)), "on_size_changed")
+
+    def _tile(self, tile):
+        if tile is None:
+            return Rect(0, 0, 0, 0), self.width, self.height
+        x, y, w, h = tile
+        return Rect(x, y, w, h), w, h
+
+    def on_render(self, tile=None, want_hit_ids=False, out=None):
+        """Render and copy to HOST memory: returns (rgba8[h,w,4] uint8, hit_ids[h,w] uint32 | None)."""
+        rect, w, h = self._tile(tile)
+        img = out if out is not None else np.empty((h, w, 4), dtype=np.uint8)
+        ids = np.empty((h, w), dtype=np.uint32) if want_hit_ids else None
+        check(self._lib.gprt_renderer_on_render(self._h, rect, img.ctypes.data, ids.ctypes.data if ids is not None else None), "on_render")
+        return img, ids
+
+    def do_raytracing(self, d_rgba8_ptr, tile=None, d_hit_ids_ptr=None, d_rgba_f32_ptr=None):
+        """Asynchronous dispatch into caller-owned DEVICE memory (raw device pointers)."""
+        rect, _, _ = self._tile(tile)
+        check(self._lib.gprt_renderer_do_raytracing(self._h, rect, d_rgba8_ptr, d_hit_ids_ptr, d_rgba_f32_ptr), "do_raytracing")
+
+    def sync(self):
+        check(self._lib.gprt_sync(self.context), "sync")
+
+    @property
+    def context(self):
+        return self._lib.gprt_renderer_context(self._h)
+
+    def set_stream(self, cuda_stream_ptr):
+        check(self._lib.gprt_set_stream(self.context, cuda_stream_ptr), "set_stream")
+
+    def counters(self) -> Counters:
+        c = Counters()
+        check(self._lib.gprt_get_counters(self.context, C.byref(c)), "get_counters")
+        return c
+
+    def timing(self) -> Timing:
+        t = Timing()
+        check(self._lib.gprt_last_timing(self.context, C.byref(t)), "last_timing")
+        return t
+
+    def launch_count(self) -> int:
+        return int(self._lib.gprt_last_launch_count(self.context))
+
+    def primary_mrays_per_s(self) -> float:
+        return float(self._lib.gprt_renderer_primary_mrays_per_s(self._h))
+
+    def _view(self) -> SceneView:
+        v = SceneView()
+        check(self._lib.gprt_renderer_scene(self._h, C.byref(v)), "scene")
+        return v
+
+    @property
+    def width(self):
+        return self._view().width
+
+    @property
+    def height(self):
+        return self._view().height
+
+    def scene(self) -> SceneData:
+        v = self._view()
+        va = _capi.view_array
+        cfg = Config()
+        C.memmove(C.byref(cfg), C.byref(v.config), C.sizeof(Config))
+        return SceneData(
+            width=v.width, height=v.height, config=cfg,
+            scene_cb=va(v.scene_cb, 1, _capi.SCENE_CB_DTYPE),
+            per_frame=va(v.per_frame, v.n_per_frame, _capi.PER_FRAME_DTYPE),
+            aabbs=va(v.aabbs, v.n_aabbs, _capi.AABB_DTYPE),
+            hit_groups=va(v.hit_groups, v.n_hit_groups, _capi.HIT_GROUP_DTYPE),
+            vertices=va(v.vertices, v.n_vertices, _capi.VERTEX_DTYPE),
+            indices=va(v.indices, v.n_indices, np.dtype("<u2")),
+            instances=va(v.instances, v.n_instances, _capi.INSTANCE_DTYPE),
+        )
+
+    def on_destroy(self):
+        if self._h:
+            self._lib.gprt_renderer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    close = on_destroy
+
+    def __del__(self):
+        try:
+            self.on_destroy()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.on_destroy()
+
+
+def write_ppm(path, rgba8: np.ndarray):
+    h, w = rgba8.shape[:2]
+    a = np.ascontiguousarray(rgba8)
+    check(lib().gprt_write_ppm(str(path).encode(), a.ctypes.data, w, h), "write_ppm")

@@ -1,0 +1,74 @@
+/*
+ * gprt_host.h -- C wrappers over the headless C++ Renderer (gpuraytracer_b200/host/renderer.h),
+ * the host side that replaces the reference's Renderer / DeviceResources / Window trio
+ * (src/Renderer.h:24-28 on_init / on_update / on_render / on_size_changed / on_destroy).
+ * Used by the Python bindings (tests, bench.py) and the gprt_render CLI.
+ */
+#ifndef GPRT_HOST_H
+#define GPRT_HOST_H
+
+#include "gprt.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gprt_renderer gprt_renderer;
+
+/* Read-only view of the scene state the renderer would hand to gprt_set_geometry /
+ * gprt_set_hit_group_table / gprt_dispatch.  Pointers stay valid until the next call on the
+ * renderer. */
+typedef struct gprt_scene_view {
+    uint32_t width, height;
+    gprt_config config;
+    const gprt_scene_cb* scene_cb;
+    const gprt_prim_per_frame* per_frame;
+    uint32_t n_per_frame;
+    const gprt_aabb* aabbs;
+    uint32_t n_aabbs;
+    const gprt_hit_group_record* hit_groups;
+    uint32_t n_hit_groups;
+    const gprt_vertex* vertices;
+    uint32_t n_vertices;
+    const uint16_t* indices;
+    uint32_t n_indices;
+    const gprt_instance_desc* instances;
+    uint32_t n_instances;
+} gprt_scene_view;
+
+/* scene_id: 0 = reference scene, 1..5 = BASELINE configs, 6 = config 3 with the long march
+ * budget.  width/height 0 = the config's own size.  grid_n: config-5 grid edge (0 = 1000).
+ * device < 0 builds the scene only (no CUDA context; on_render then fails with
+ * GPRT_E_NO_DEVICE) -- that is how CPU-only tests obtain scene data for the oracle. */
+int gprt_renderer_create(gprt_renderer** out, int scene_id, uint32_t width, uint32_t height,
+                         uint32_t grid_n, int device, const gprt_config* config_override);
+void gprt_renderer_destroy(gprt_renderer* r);
+
+/* Renderer::on_init: device objects, geometry upload, acceleration structures. */
+int gprt_renderer_on_init(gprt_renderer* r);
+/* Renderer::on_update with the StepTimer replaced by an explicit animation time; the optional
+ * camera/light orbits (src/Renderer.cpp:92-110) take degrees for this update. */
+int gprt_renderer_on_update(gprt_renderer* r, float animate_geometry_time,
+                            float camera_orbit_deg, float light_orbit_deg);
+/* Renderer::on_render: do_raytracing over `tile` (w == 0: whole image) and, instead of the copy
+ * to the swap chain, an optional copy to host memory (tile-packed RGBA8 / hit ids). */
+int gprt_renderer_on_render(gprt_renderer* r, gprt_rect tile, void* h_rgba8, uint32_t* h_hit_ids);
+/* do_raytracing only, output left in device memory (tile-packed); asynchronous. */
+int gprt_renderer_do_raytracing(gprt_renderer* r, gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids,
+                                float* d_rgba_f32);
+int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);
+
+int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out);
+gprt_ctx* gprt_renderer_context(gprt_renderer* r);
+
+/* Frame statistics in the reference's convention (calculate_frame_stats,
+ * src/Renderer.cpp:375-399): million PRIMARY rays per second from the last GPU dispatch time. */
+float gprt_renderer_primary_mrays_per_s(gprt_renderer* r);
+
+/* Write a tile-packed RGBA8 buffer as a binary PPM (the headless stand-in for Present). */
+int gprt_write_ppm(const char* path, const void* rgba8, uint32_t width, uint32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPRT_HOST_H */
