@@ -14,6 +14,8 @@ LIB_PATH = os.path.join(_HERE, "libgprt.so")
 GPRT_ABI_VERSION = 1
 GPRT_MATH_PARITY, GPRT_MATH_FAST = 0, 1
 GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1
+GPRT_FLAG_PROFILE_KERNELS = 2
+GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14
 GPRT_HIT_MISS = 0xFFFFFFFF
 GPRT_HIT_TRIANGLE = 0x00000000
 GPRT_HIT_AABB = 0x10000000
@@ -37,6 +39,10 @@ class Rect(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("radiance_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("candidates", C.c_uint64 * 3),
                 ("bvh_node_visits", C.c_uint64), ("queue_overflow", C.c_uint64)]
+
+
+class KernelProfile(C.Structure):
+    _fields_ = [("ms", C.c_float * 14), ("launches", C.c_uint32 * 14), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
 
 
 class Timing(C.Structure):
@@ -93,6 +99,8 @@ def lib():
         "gprt_sync": (i32, [vp]),
         "gprt_get_counters": (i32, [vp, C.POINTER(Counters)]),
         "gprt_last_timing": (i32, [vp, C.POINTER(Timing)]),
+        "gprt_get_kernel_profile": (i32, [vp, C.POINTER(KernelProfile)]),
+        "gprt_measure_fp32_peak": (i32, [vp, C.POINTER(C.c_float)]),
         "gprt_last_cuda_error": (i32, [vp]),
         "gprt_set_stream": (i32, [vp, vp]),
         "gprt_last_launch_count": (i32, [vp]),
@@ -121,7 +129,7 @@ def lib():
 EXPORTED_SYMBOLS = [
     "gprt_default_config", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
     "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_host", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
-    "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
+    "gprt_get_kernel_profile", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
     "gprt_renderer_do_raytracing", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",

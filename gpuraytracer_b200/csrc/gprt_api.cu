@@ -1,0 +1,626 @@
+// gprt_api.cu -- the C ABI of include/gprt.h: context, geometry upload, LBVH build, dispatch.
+// No torch, no C++ types across the boundary, no exceptions, and no CPU render path: without a
+// CUDA device gprt_create fails with GPRT_E_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/gprt.h"
+#include "lbvh.h"
+#include "wavefront.cuh"
+
+using namespace gprt;
+
+namespace {
+
+constexpr uint32_t kDefaultPassPixels = 1u << 22; // pixels per internal pass (bounds queue memory)
+constexpr int kStagingSlots = 3;                  // == frame_count of the reference (src/Renderer.h:92)
+constexpr int kMaxBands = 256;
+
+struct HostCtrlCopy { WaveCtrl ctrl[kMaxDepth + 2]; };
+
+} // namespace
+
+struct gprt_ctx {
+    int device = 0;
+    gprt_config cfg;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int last_cuda_error = 0;
+    const KernelTable* kt = nullptr;       // traverse / resolve / shade_spawn / final: always the IEEE build
+    const KernelTable* kt_isect = nullptr; // intersection (march) kernels: IEEE or fast-math build
+
+    // host copies of the static scene
+    std::vector<gprt_aabb> h_aabbs;
+    std::vector<gprt_vertex> h_vertices;
+    std::vector<uint16_t> h_indices;
+    std::vector<gprt_hit_group_record> h_records;
+    gprt_instance_desc h_instances[2];
+    bool have_tri_instance = false, have_aabb_instance = false, have_geometry = false, have_table = false;
+    uint32_t tri_contrib = 0, aabb_contrib = 2;
+
+    // device scene
+    float* d_aabbs = nullptr;
+    PrimRecord* d_prims = nullptr;
+    float* d_per_frame = nullptr;
+    uint32_t per_frame_capacity = 0;
+    float* d_tri_pos = nullptr;
+    float* d_tri_nrm = nullptr;
+    float4* d_nodes = nullptr;
+    uint32_t* d_sorted = nullptr;
+    void* d_lbvh_scratch = nullptr;
+    SceneDev scene;
+    uint32_t type_mask = 0;
+    uint32_t max_instance_index = 0;
+    bool built = false;
+
+    // pass buffers
+    uint32_t pass_pixels = 0;
+    uint32_t pass_depth = 0;
+    uint32_t pass_type_mask = 0;
+    uint32_t cand_capacity = 0;
+    WaveBuffers wb;
+    std::vector<void*> pass_allocs;
+
+    // per-frame upload staging
+    void* h_staging[kStagingSlots] = {nullptr, nullptr, nullptr};
+    size_t staging_bytes = 0;
+    cudaEvent_t staging_done[kStagingSlots] = {nullptr, nullptr, nullptr};
+    int staging_next = 0;
+
+    // internal framebuffer for gprt_dispatch_host
+    uint8_t* d_fb = nullptr;
+    uint32_t* d_fb_ids = nullptr;
+    size_t fb_pixels = 0;
+
+    // stats
+    HostCtrlCopy* h_ctrl = nullptr; // pinned, [kMaxBands]
+    int n_bands_last = 0;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_build0 = nullptr, ev_build1 = nullptr;
+    bool have_dispatch_timing = false, have_build_timing = false;
+    int last_launches = 0;
+    uint32_t last_depth = 0;
+
+    // per-kernel profiling (GPRT_FLAG_PROFILE_KERNELS)
+    struct Interval { int kind; cudaEvent_t e0, e1; };
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    std::vector<Interval> intervals;
+};
+
+namespace {
+
+#define GPRT_CUDA(ctx, expr)                                                          \
+    do {                                                                              \
+        cudaError_t e__ = (expr);                                                     \
+        if (e__ != cudaSuccess) {                                                     \
+            (ctx)->last_cuda_error = (int)e__;                                        \
+            return e__ == cudaErrorMemoryAllocation ? GPRT_E_OUT_OF_MEMORY : GPRT_E_CUDA; \
+        }                                                                             \
+    } while (0)
+
+void invert_affine_3x4(const float in[3][4], float out[12]) {
+    double r[3][3], t[3];
+    for (int i = 0; i < 3; i++) { for (int j = 0; j < 3; j++) r[i][j] = in[i][j]; t[i] = in[i][3]; }
+    const double det = r[0][0] * (r[1][1] * r[2][2] - r[1][2] * r[2][1]) - r[0][1] * (r[1][0] * r[2][2] - r[1][2] * r[2][0]) +
+                       r[0][2] * (r[1][0] * r[2][1] - r[1][1] * r[2][0]);
+    double inv[3][3];
+    inv[0][0] = (r[1][1] * r[2][2] - r[1][2] * r[2][1]) / det;
+    inv[0][1] = (r[0][2] * r[2][1] - r[0][1] * r[2][2]) / det;
+    inv[0][2] = (r[0][1] * r[1][2] - r[0][2] * r[1][1]) / det;
+    inv[1][0] = (r[1][2] * r[2][0] - r[1][0] * r[2][2]) / det;
+    inv[1][1] = (r[0][0] * r[2][2] - r[0][2] * r[2][0]) / det;
+    inv[1][2] = (r[0][2] * r[1][0] - r[0][0] * r[1][2]) / det;
+    inv[2][0] = (r[1][0] * r[2][1] - r[1][1] * r[2][0]) / det;
+    inv[2][1] = (r[0][1] * r[2][0] - r[0][0] * r[2][1]) / det;
+    inv[2][2] = (r[0][0] * r[1][1] - r[0][1] * r[1][0]) / det;
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) out[4 * i + j] = (float)inv[i][j];
+        out[4 * i + 3] = (float)(-(inv[i][0] * t[0] + inv[i][1] * t[1] + inv[i][2] * t[2]));
+    }
+}
+
+Material to_material(const gprt_material& m) {
+    Material r;
+    for (int i = 0; i < 4; i++) r.albedo[i] = m.albedo[i];
+    r.reflectance_coefficient = m.reflectance_coefficient;
+    r.diffuse_coefficient = m.diffuse_coefficient;
+    r.specular_coefficient = m.specular_coefficient;
+    r.specular_power = m.specular_power;
+    r.step_scale = m.step_scale;
+    return r;
+}
+
+void free_pass_buffers(gprt_ctx* c) {
+    for (void* p : c->pass_allocs) cudaFree(p);
+    c->pass_allocs.clear();
+    c->pass_pixels = 0;
+    std::memset(&c->wb, 0, sizeof c->wb);
+}
+
+template <class T> int alloc_pass(gprt_ctx* c, T** out, size_t count) {
+    void* p = nullptr;
+    GPRT_CUDA(c, cudaMalloc(&p, count * sizeof(T) + 256));
+    c->pass_allocs.push_back(p);
+    *out = (T*)p;
+    return GPRT_OK;
+}
+
+int ensure_pass_buffers(gprt_ctx* c, uint32_t pixels) {
+    const uint32_t depth = c->cfg.max_recursion_depth;
+    if (c->pass_pixels >= pixels && c->pass_depth >= depth && c->pass_type_mask == c->type_mask) return GPRT_OK;
+    cudaStreamSynchronize(c->stream);
+    free_pass_buffers(c);
+    const size_t P = pixels, R = 2 * P;
+    const uint32_t per_ray = c->cfg.cand_per_ray ? c->cfg.cand_per_ray : 2u;
+    const size_t cap = R * per_ray;
+    int rc;
+#define A(ptr, n) if ((rc = alloc_pass(c, &(ptr), (n))) != GPRT_OK) { free_pass_buffers(c); return rc; }
+    for (int q = 0; q < 2; q++) { A(c->wb.ray_o[q], R); A(c->wb.ray_d[q], R); }
+    A(c->wb.ray_tcur, R);
+    A(c->wb.hitkey, R);
+    A(c->wb.hit_n, R);
+    for (int t = 0; t < kNumTypes; t++) {
+        if (!((c->type_mask >> t) & 1u)) continue;
+        A(c->wb.cand[t], cap);
+        A(c->wb.cand_res[t], cap);
+    }
+    A(c->wb.ctrl, (size_t)(kMaxDepth + 2));
+    A(c->wb.lvl_o_t, P * depth);
+    A(c->wb.lvl_d, P * depth);
+    A(c->wb.lvl_n, P * depth);
+    A(c->wb.lvl_code, P * depth);
+    A(c->wb.lvl_shadow, P * depth);
+#undef A
+    c->pass_pixels = pixels;
+    c->pass_depth = depth;
+    c->pass_type_mask = c->type_mask;
+    c->cand_capacity = (uint32_t)(cap > 0xFFFFFFF0ull ? 0xFFFFFFF0ull : cap);
+    return GPRT_OK;
+}
+
+int upload_static_scene(gprt_ctx* c) {
+    const uint32_t n = (uint32_t)c->h_aabbs.size();
+    // primitive records from the hit-group table: record index = rayType + 2*geometryIndex + contribution
+    std::vector<PrimRecord> prims(n);
+    c->type_mask = 0;
+    c->max_instance_index = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const size_t ri = (size_t)c->aabb_contrib + 2 * (size_t)i;
+        if (ri >= c->h_records.size()) return GPRT_E_INVALID_ARG;
+        const gprt_hit_group_record& rec = c->h_records[ri];
+        PrimRecord& p = prims[i];
+        std::memset(&p, 0, sizeof p);
+        p.mat = to_material(rec.material_cb);
+        p.instance_index = rec.aabb_cb.instance_index;
+        if (p.instance_index > c->max_instance_index) c->max_instance_index = p.instance_index;
+        switch (rec.shader_id[0]) {
+        case GPRT_HG_AABB_ANALYTIC: if (rec.aabb_cb.primitive_type >= GPRT_ANALYTIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = rec.aabb_cb.primitive_type; break;
+        case GPRT_HG_AABB_VOLUMETRIC: if (rec.aabb_cb.primitive_type >= GPRT_VOLUMETRIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 2; break;
+        case GPRT_HG_AABB_SDF: if (rec.aabb_cb.primitive_type >= GPRT_SDF_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 3 + rec.aabb_cb.primitive_type; break;
+        default: return GPRT_E_INVALID_ARG;
+        }
+        c->type_mask |= 1u << p.type_id;
+    }
+    // triangles: positions per triangle + the normal of the vertex indices[0] names (src/Raytracing.hlsl:184)
+    const uint32_t n_tris = c->have_tri_instance ? (uint32_t)(c->h_indices.size() / 3) : 0;
+    std::vector<float> tri_pos(9 * (size_t)n_tris), tri_nrm(3 * (size_t)n_tris);
+    for (uint32_t t = 0; t < n_tris; t++) {
+        for (int k = 0; k < 3; k++) {
+            const uint16_t vi = c->h_indices[3 * t + k];
+            if (vi >= c->h_vertices.size()) return GPRT_E_INVALID_ARG;
+            for (int a = 0; a < 3; a++) tri_pos[9 * t + 3 * k + a] = c->h_vertices[vi].position[a];
+        }
+        for (int a = 0; a < 3; a++) tri_nrm[3 * t + a] = c->h_vertices[c->h_indices[3 * t]].normal[a];
+    }
+    if (n_tris && c->tri_contrib >= c->h_records.size()) return GPRT_E_INVALID_ARG;
+
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
+    cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch);
+    c->d_aabbs = nullptr; c->d_prims = nullptr; c->d_tri_pos = c->d_tri_nrm = nullptr; c->d_nodes = nullptr; c->d_sorted = nullptr; c->d_lbvh_scratch = nullptr;
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_aabbs, (size_t)(n ? n : 1) * 6 * sizeof(float)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_prims, (size_t)(n ? n : 1) * sizeof(PrimRecord)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_pos, (tri_pos.size() + 1) * sizeof(float)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_nrm, (tri_nrm.size() + 1) * sizeof(float)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_nodes, (size_t)(n ? n : 1) * 4 * sizeof(float4)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_sorted, (size_t)(n ? n : 1) * sizeof(uint32_t)));
+    GPRT_CUDA(c, cudaMalloc(&c->d_lbvh_scratch, lbvh_scratch_bytes(n ? n : 1)));
+    if (n) {
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_prims, prims.data(), (size_t)n * sizeof(PrimRecord), cudaMemcpyHostToDevice, c->stream));
+    }
+    if (n_tris) {
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_pos, tri_pos.data(), tri_pos.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_nrm, tri_nrm.data(), tri_nrm.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    }
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream)); // the host vectors above go out of scope
+
+    SceneDev& s = c->scene;
+    std::memset(&s, 0, sizeof s);
+    s.bvh_nodes = c->d_nodes;
+    s.n_prims = n;
+    s.aabbs = c->d_aabbs;
+    s.prims = c->d_prims;
+    s.per_frame = nullptr;
+    s.tri_pos = c->d_tri_pos;
+    s.tri_nrm = c->d_tri_nrm;
+    s.n_tris = n_tris;
+    s.has_aabb_instance = c->have_aabb_instance ? 1u : 0u;
+    if (c->have_tri_instance) invert_affine_3x4(c->h_instances[0].transform, s.tri_w2o);
+    if (c->have_aabb_instance) {
+        invert_affine_3x4(c->h_instances[1].transform, s.aabb_w2o);
+        std::memcpy(s.aabb_o2w, c->h_instances[1].transform, sizeof s.aabb_o2w);
+    }
+    if (n_tris) s.plane_mat = to_material(c->h_records[c->tri_contrib].material_cb);
+    return GPRT_OK;
+}
+
+cudaEvent_t take_event(gprt_ctx* c) {
+    if (c->ev_used == c->ev_pool.size()) {
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+        c->ev_pool.push_back(e);
+    }
+    return c->ev_pool[c->ev_used++];
+}
+
+struct ScopedInterval { // CUDA events around one launch when profiling is on
+    gprt_ctx* c;
+    cudaEvent_t e1 = nullptr;
+    ScopedInterval(gprt_ctx* ctx, int kind) : c(ctx) {
+        if (!(c->cfg.flags & GPRT_FLAG_PROFILE_KERNELS)) return;
+        cudaEvent_t e0 = take_event(c);
+        e1 = take_event(c);
+        if (!e0 || !e1) { e1 = nullptr; return; }
+        cudaEventRecord(e0, c->stream);
+        c->intervals.push_back({kind, e0, e1});
+    }
+    ~ScopedInterval() { if (e1) cudaEventRecord(e1, c->stream); }
+};
+
+int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t height, gprt_rect pass, const OutputBuffers& ob, int band) {
+    PassParams pp;
+    std::memset(&pp, 0, sizeof pp);
+    std::memcpy(pp.fc.projection_to_world, cb->projection_to_world, sizeof pp.fc.projection_to_world);
+    std::memcpy(pp.fc.camera_position, cb->camera_position, 16);
+    std::memcpy(pp.fc.light_position, cb->light_position, 16);
+    std::memcpy(pp.fc.light_ambient_color, cb->light_ambient_color, 16);
+    std::memcpy(pp.fc.light_diffuse_color, cb->light_diffuse_color, 16);
+    pp.fc.elapsed_time = cb->elapsed_time;
+    pp.fc.width = width;
+    pp.fc.height = height;
+    pp.tile_x = pass.x; pp.tile_y = pass.y; pp.tile_w = pass.w; pp.tile_h = pass.h;
+    pp.n_pixels = pass.w * pass.h;
+    pp.max_depth = c->cfg.max_recursion_depth;
+    pp.metaball_max_steps = c->cfg.metaball_max_steps;
+    pp.sdf_max_steps = c->cfg.sdf_max_steps;
+    pp.ray_capacity = 2 * pp.n_pixels;
+    pp.cand_capacity = c->cand_capacity;
+    pp.brute_force = (c->cfg.flags & GPRT_FLAG_BRUTE_FORCE_TRAVERSAL) ? 1u : 0u;
+
+    const uint32_t D = pp.max_depth;
+    GPRT_CUDA(c, cudaMemsetAsync(c->wb.ctrl, 0, sizeof(WaveCtrl) * (kMaxDepth + 2), c->stream));
+    if (D > 1) GPRT_CUDA(c, cudaMemsetAsync(c->wb.lvl_code + pp.n_pixels, 0xFE, sizeof(uint32_t) * (size_t)pp.n_pixels * (D - 1), c->stream));
+    int launches = 0;
+    for (uint32_t wave = 1; wave <= D; wave++) {
+        { ScopedInterval si(c, GPRT_K_TRAVERSE); launches += c->kt->traverse(c->scene, pp, c->wb, (int)wave, c->stream); }
+        for (int t = 0; t < kNumTypes; t++)
+            if ((c->type_mask >> t) & 1u) {
+                ScopedInterval si(c, GPRT_K_INTERSECT0 + t);
+                launches += c->kt_isect->intersect(c->scene, pp, c->wb, (int)wave, t, (int)c->cfg.metaballs_count, c->stream);
+            }
+        if (c->type_mask) { ScopedInterval si(c, GPRT_K_RESOLVE); launches += c->kt->resolve(c->scene, pp, c->wb, (int)wave, c->type_mask, c->stream); }
+        { ScopedInterval si(c, GPRT_K_SHADE_SPAWN); launches += c->kt->shade_spawn(c->scene, pp, c->wb, (int)wave, c->stream); }
+    }
+    { ScopedInterval si(c, GPRT_K_FINAL); launches += c->kt->final_color(c->scene, pp, c->wb, ob, c->stream); }
+    GPRT_CUDA(c, cudaGetLastError());
+    if (band < kMaxBands) GPRT_CUDA(c, cudaMemcpyAsync(&c->h_ctrl[band], c->wb.ctrl, sizeof(HostCtrlCopy), cudaMemcpyDeviceToHost, c->stream));
+    c->last_launches += launches;
+    return GPRT_OK;
+}
+
+int check_overflow(gprt_ctx* c) {
+    for (int b = 0; b < c->n_bands_last && b < kMaxBands; b++)
+        for (uint32_t w = 1; w <= c->last_depth; w++) {
+            const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
+            if (wc.overflow) return GPRT_E_QUEUE_OVERFLOW;
+        }
+    return GPRT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
+    if (!out) return GPRT_E_INVALID_ARG;
+    *out = nullptr;
+    gprt_config c0;
+    gprt_default_config(&c0);
+    if (cfg) c0 = *cfg;
+    if (c0.abi_version != GPRT_ABI_VERSION) return GPRT_E_ABI_MISMATCH;
+    if (c0.max_recursion_depth < 1 || c0.max_recursion_depth > (uint32_t)kMaxDepth) return GPRT_E_UNSUPPORTED;
+    if (c0.metaballs_count != 3 && c0.metaballs_count != 5) return GPRT_E_UNSUPPORTED;
+    if (c0.metaball_max_steps == 0 || c0.sdf_max_steps == 0) return GPRT_E_INVALID_ARG;
+    if (c0.math_mode != GPRT_MATH_PARITY && c0.math_mode != GPRT_MATH_FAST) return GPRT_E_INVALID_ARG;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
+    if (device_ordinal < 0 || device_ordinal >= n_dev) return GPRT_E_NO_DEVICE;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_ordinal) != cudaSuccess) return GPRT_E_NO_DEVICE;
+    if (prop.major != 10) return GPRT_E_NO_DEVICE; // the kernels are built for sm_100a only
+    gprt_ctx* c = new (std::nothrow) gprt_ctx();
+    if (!c) return GPRT_E_OUT_OF_MEMORY;
+    c->device = device_ordinal;
+    c->cfg = c0;
+    // Fast mode only swaps the march kernels, where the time goes.  Camera rays, the checker
+    // filter and shading stay IEEE: their cancellations (ray differentials, frac/floor at the grid
+    // lines) do not survive approximate division.
+    c->kt = kernels_parity();
+    c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : kernels_parity();
+    std::memset(&c->scene, 0, sizeof c->scene);
+    std::memset(&c->wb, 0, sizeof c->wb);
+    std::memset(c->h_instances, 0, sizeof c->h_instances);
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) { delete c; return GPRT_E_NO_DEVICE; }
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    c->own_stream = ok;
+    ok = ok && cudaEventCreate(&c->ev_start) == cudaSuccess && cudaEventCreate(&c->ev_stop) == cudaSuccess &&
+         cudaEventCreate(&c->ev_build0) == cudaSuccess && cudaEventCreate(&c->ev_build1) == cudaSuccess;
+    for (int i = 0; ok && i < kStagingSlots; i++) ok = cudaEventCreateWithFlags(&c->staging_done[i], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaMallocHost((void**)&c->h_ctrl, sizeof(HostCtrlCopy) * kMaxBands) == cudaSuccess;
+    if (!ok) { c->last_cuda_error = (int)cudaGetLastError(); gprt_destroy(c); return GPRT_E_CUDA; }
+    std::memset(c->h_ctrl, 0, sizeof(HostCtrlCopy) * kMaxBands);
+    *out = c;
+    return GPRT_OK;
+}
+
+void gprt_destroy(gprt_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_pass_buffers(c);
+    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_per_frame); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
+    cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_fb); cudaFree(c->d_fb_ids);
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
+    for (int i = 0; i < kStagingSlots; i++) {
+        if (c->h_staging[i]) cudaFreeHost(c->h_staging[i]);
+        if (c->staging_done[i]) cudaEventDestroy(c->staging_done[i]);
+    }
+    if (c->h_ctrl) cudaFreeHost(c->h_ctrl);
+    if (c->ev_start) cudaEventDestroy(c->ev_start);
+    if (c->ev_stop) cudaEventDestroy(c->ev_stop);
+    if (c->ev_build0) cudaEventDestroy(c->ev_build0);
+    if (c->ev_build1) cudaEventDestroy(c->ev_build1);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int gprt_set_stream(gprt_ctx* c, void* cuda_stream) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)cuda_stream;
+    c->own_stream = false;
+    return GPRT_OK;
+}
+
+int gprt_set_geometry(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs, const gprt_vertex* vertices, uint32_t n_vertices,
+                      const uint16_t* indices, uint32_t n_indices, const gprt_instance_desc* instances, uint32_t n_instances) {
+    if (!c || (n_aabbs && !aabbs) || (n_vertices && !vertices) || (n_indices && !indices) || (n_instances && !instances)) return GPRT_E_INVALID_ARG;
+    if (n_indices % 3 != 0) return GPRT_E_INVALID_ARG;
+    if (n_aabbs >= (1u << 28)) return GPRT_E_UNSUPPORTED;
+    if (n_instances > 2) return GPRT_E_UNSUPPORTED; // the reference's TLAS: one triangle BLAS instance + one AABB BLAS instance
+    c->have_tri_instance = c->have_aabb_instance = false;
+    for (uint32_t i = 0; i < n_instances; i++) {
+        const uint32_t contrib = instances[i].hit_group_contrib_and_flags & 0xFFFFFFu;
+        if (instances[i].acceleration_structure == GPRT_BLAS_TRIANGLES) {
+            if (c->have_tri_instance) return GPRT_E_UNSUPPORTED;
+            c->h_instances[0] = instances[i]; c->have_tri_instance = n_indices >= 3; c->tri_contrib = contrib;
+        } else if (instances[i].acceleration_structure == GPRT_BLAS_AABBS) {
+            if (c->have_aabb_instance) return GPRT_E_UNSUPPORTED;
+            c->h_instances[1] = instances[i]; c->have_aabb_instance = n_aabbs > 0; c->aabb_contrib = contrib;
+        } else return GPRT_E_INVALID_ARG;
+    }
+    c->h_aabbs.assign(aabbs, aabbs + n_aabbs);
+    c->h_vertices.assign(vertices, vertices + n_vertices);
+    c->h_indices.assign(indices, indices + n_indices);
+    c->have_geometry = true;
+    c->built = false;
+    return GPRT_OK;
+}
+
+int gprt_set_hit_group_table(gprt_ctx* c, const void* records, uint32_t n_records, uint32_t stride_bytes) {
+    if (!c || !records || stride_bytes < sizeof(gprt_hit_group_record)) return GPRT_E_INVALID_ARG;
+    c->h_records.resize(n_records);
+    for (uint32_t i = 0; i < n_records; i++) std::memcpy(&c->h_records[i], (const char*)records + (size_t)i * stride_bytes, sizeof(gprt_hit_group_record));
+    c->have_table = true;
+    c->built = false;
+    return GPRT_OK;
+}
+
+int gprt_build_accel(gprt_ctx* c) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    if (!c->have_geometry || !c->have_table) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    int rc = upload_static_scene(c);
+    if (rc != GPRT_OK) return rc;
+    GPRT_CUDA(c, cudaEventRecord(c->ev_build0, c->stream));
+    int32_t root = INT32_MIN;
+    lbvh_build(c->d_aabbs, c->scene.n_prims, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, &root, c->stream);
+    GPRT_CUDA(c, cudaEventRecord(c->ev_build1, c->stream));
+    GPRT_CUDA(c, cudaGetLastError());
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream)); // blocking, like wait_for_gpu at src/Renderer.cpp:827
+    c->scene.root_ref = root;
+    c->have_build_timing = true;
+    c->built = true;
+    return GPRT_OK;
+}
+
+int gprt_refit_accel(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs) {
+    if (!c || !aabbs) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    if (n_aabbs != c->scene.n_prims) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    c->h_aabbs.assign(aabbs, aabbs + n_aabbs);
+    GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n_aabbs * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
+    lbvh_refit(c->d_aabbs, n_aabbs, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, c->stream);
+    GPRT_CUDA(c, cudaGetLastError());
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GPRT_OK;
+}
+
+int gprt_dispatch(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                  uint32_t height, gprt_rect tile, void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids, float* d_rgba_f32) {
+    if (!c || !scene || !d_rgba8 || width == 0 || height == 0) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    if (tile.w == 0 || tile.h == 0 || tile.x + tile.w > width || tile.y + tile.h > height) return GPRT_E_INVALID_ARG;
+    if (pitch_bytes < (size_t)tile.w * 4 || (pitch_bytes & 3u)) return GPRT_E_INVALID_ARG;
+    if (n_per_frame && !per_frame) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+
+    // every primitive's instance_index must address the uploaded transforms
+    if (c->scene.n_prims && n_per_frame <= c->max_instance_index) return GPRT_E_INVALID_ARG;
+
+    // per-frame transforms: host -> pinned staging -> device (src/Renderer.cpp:438-443)
+    if (n_per_frame) {
+        const size_t bytes = (size_t)n_per_frame * sizeof(gprt_prim_per_frame);
+        if (c->per_frame_capacity < n_per_frame) {
+            cudaStreamSynchronize(c->stream);
+            cudaFree(c->d_per_frame); c->d_per_frame = nullptr;
+            GPRT_CUDA(c, cudaMalloc((void**)&c->d_per_frame, bytes));
+            c->per_frame_capacity = n_per_frame;
+        }
+        if (c->staging_bytes < bytes) {
+            cudaStreamSynchronize(c->stream);
+            for (int i = 0; i < kStagingSlots; i++) { if (c->h_staging[i]) cudaFreeHost(c->h_staging[i]); c->h_staging[i] = nullptr; }
+            for (int i = 0; i < kStagingSlots; i++) GPRT_CUDA(c, cudaMallocHost(&c->h_staging[i], bytes));
+            c->staging_bytes = bytes;
+        }
+        const int slot = c->staging_next;
+        c->staging_next = (slot + 1) % kStagingSlots;
+        GPRT_CUDA(c, cudaEventSynchronize(c->staging_done[slot]));
+        std::memcpy(c->h_staging[slot], per_frame, bytes);
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_per_frame, c->h_staging[slot], bytes, cudaMemcpyHostToDevice, c->stream));
+        GPRT_CUDA(c, cudaEventRecord(c->staging_done[slot], c->stream));
+    }
+    c->scene.per_frame = c->d_per_frame;
+
+    // internal passes bound the queue memory: at most kDefaultPassPixels pixels each
+    const uint64_t tile_pixels = (uint64_t)tile.w * tile.h;
+    uint32_t band_h = tile.h;
+    if (tile_pixels > kDefaultPassPixels) { band_h = kDefaultPassPixels / tile.w; if (band_h == 0) band_h = 1; }
+    if ((uint64_t)band_h * tile.w >= (1u << 26)) return GPRT_E_UNSUPPORTED;
+    int rc = ensure_pass_buffers(c, band_h * tile.w);
+    if (rc != GPRT_OK) return rc;
+
+    c->last_launches = 0;
+    c->last_depth = c->cfg.max_recursion_depth;
+    c->ev_used = 0;
+    c->intervals.clear();
+    GPRT_CUDA(c, cudaEventRecord(c->ev_start, c->stream));
+    int band = 0;
+    for (uint32_t y0 = 0; y0 < tile.h; y0 += band_h, band++) {
+        gprt_rect pass = {tile.x, tile.y + y0, tile.w, (tile.h - y0 < band_h) ? tile.h - y0 : band_h};
+        OutputBuffers ob;
+        ob.rgba8 = (uint8_t*)d_rgba8; ob.pitch = pitch_bytes; ob.hit_ids = d_hit_ids; ob.rgba_f32 = (float4*)d_rgba_f32;
+        ob.out_x0 = 0; ob.out_y0 = y0; ob.out_w = tile.w;
+        rc = run_pass(c, scene, width, height, pass, ob, band);
+        if (rc != GPRT_OK) return rc;
+    }
+    c->n_bands_last = band;
+    GPRT_CUDA(c, cudaEventRecord(c->ev_stop, c->stream));
+    c->have_dispatch_timing = true;
+    return GPRT_OK;
+}
+
+int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                       uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
+    if (!c || !h_rgba8) return GPRT_E_INVALID_ARG;
+    if (tile.w == 0 || tile.h == 0) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    const size_t pixels = (size_t)tile.w * tile.h;
+    if (c->fb_pixels < pixels) {
+        cudaStreamSynchronize(c->stream);
+        cudaFree(c->d_fb); cudaFree(c->d_fb_ids); c->d_fb = nullptr; c->d_fb_ids = nullptr; c->fb_pixels = 0;
+        GPRT_CUDA(c, cudaMalloc((void**)&c->d_fb, pixels * 4));
+        GPRT_CUDA(c, cudaMalloc((void**)&c->d_fb_ids, pixels * 4));
+        c->fb_pixels = pixels;
+    }
+    int rc = gprt_dispatch(c, scene, per_frame, n_per_frame, width, height, tile, c->d_fb, (size_t)tile.w * 4, h_hit_ids ? c->d_fb_ids : nullptr, nullptr);
+    if (rc != GPRT_OK) return rc;
+    GPRT_CUDA(c, cudaMemcpy2DAsync(h_rgba8, pitch_bytes, c->d_fb, (size_t)tile.w * 4, (size_t)tile.w * 4, tile.h, cudaMemcpyDeviceToHost, c->stream));
+    if (h_hit_ids) GPRT_CUDA(c, cudaMemcpyAsync(h_hit_ids, c->d_fb_ids, pixels * 4, cudaMemcpyDeviceToHost, c->stream));
+    return gprt_sync(c);
+}
+
+int gprt_sync(gprt_ctx* c) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return check_overflow(c);
+}
+
+int gprt_get_counters(gprt_ctx* c, gprt_counters* out) {
+    if (!c || !out) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    std::memset(out, 0, sizeof *out);
+    for (int b = 0; b < c->n_bands_last && b < kMaxBands; b++)
+        for (uint32_t w = 1; w <= c->last_depth; w++) {
+            const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
+            out->radiance_rays += wc.n_radiance;
+            out->shadow_rays += wc.n_shadow;
+            out->candidates[0] += (uint64_t)wc.cand_count[0] + wc.cand_count[1];
+            out->candidates[1] += wc.cand_count[2];
+            for (int t = 3; t < kNumTypes; t++) out->candidates[2] += wc.cand_count[t];
+            out->queue_overflow += wc.overflow;
+        }
+    return GPRT_OK;
+}
+
+int gprt_last_timing(gprt_ctx* c, gprt_timing* out) {
+    if (!c || !out) return GPRT_E_INVALID_ARG;
+    out->dispatch_ms = 0.0f;
+    out->build_accel_ms = 0.0f;
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->have_dispatch_timing) GPRT_CUDA(c, cudaEventElapsedTime(&out->dispatch_ms, c->ev_start, c->ev_stop));
+    if (c->have_build_timing) GPRT_CUDA(c, cudaEventElapsedTime(&out->build_accel_ms, c->ev_build0, c->ev_build1));
+    return GPRT_OK;
+}
+
+int gprt_get_kernel_profile(gprt_ctx* c, gprt_kernel_profile* out) {
+    if (!c || !out) return GPRT_E_INVALID_ARG;
+    std::memset(out, 0, sizeof *out);
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (const gprt_ctx::Interval& iv : c->intervals) {
+        float ms = 0.0f;
+        GPRT_CUDA(c, cudaEventElapsedTime(&ms, iv.e0, iv.e1));
+        out->ms[iv.kind] += ms;
+        out->launches[iv.kind]++;
+    }
+    for (int b = 0; b < c->n_bands_last && b < kMaxBands; b++)
+        for (uint32_t w = 1; w <= c->last_depth; w++) {
+            const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
+            for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += wc.cand_count[t]; }
+        }
+    return GPRT_OK;
+}
+
+int gprt_measure_fp32_peak(gprt_ctx* c, float* tflops_out) {
+    if (!c || !tflops_out) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    double tf = 0.0;
+    const int rc = fp32_peak_probe(c->stream, &tf);
+    if (rc != 0) { c->last_cuda_error = rc; return GPRT_E_CUDA; }
+    *tflops_out = (float)tf;
+    return GPRT_OK;
+}
+
+int gprt_last_cuda_error(gprt_ctx* c) { return c ? c->last_cuda_error : 0; }
+int gprt_last_launch_count(gprt_ctx* c) { return c ? c->last_launches : 0; }
+
+} // extern "C"

@@ -1,0 +1,429 @@
+// kernels.cu -- the wavefront kernels.  Compiled twice into libgprt.so:
+//   -DGPRT_KERNELS_PARITY   --fmad=false                  (IEEE, oracle-exact arithmetic)
+//   -DGPRT_KERNELS_FAST     --use_fast_math -DGPRT_FAST_MATH
+// See wavefront.cuh for the pipeline; prims.cuh / shade.cuh for the math and the reference
+// file:line each piece follows.
+#include <cuda_runtime.h>
+
+#include "prims.cuh"
+#include "wavefront.cuh"
+
+namespace gprt {
+namespace {
+
+constexpr int kBlock = 256;
+constexpr unsigned kFull = 0xFFFFFFFFu;
+
+__device__ __forceinline__ unsigned long long pack_key(float t, uint32_t code) {
+    // t >= 0 here, so the IEEE bit pattern orders like the value; fabsf folds -0 into +0
+    return ((unsigned long long)__float_as_uint(fabsf(t)) << 32) | (unsigned long long)code;
+}
+
+__device__ __forceinline__ V3 ld3(const float4 v) { return v3(v.x, v.y, v.z); }
+
+// Canonical ray/AABB predicate: closed interval, IEEE 1/d, fminf/fmaxf.
+__device__ __forceinline__ bool slab_test(V3 o, V3 inv_d, const float* lo, const float* hi, float tmin, float tmax) {
+    const float t0x = (lo[0] - o.x) * inv_d.x, t1x = (hi[0] - o.x) * inv_d.x;
+    const float t0y = (lo[1] - o.y) * inv_d.y, t1y = (hi[1] - o.y) * inv_d.y;
+    const float t0z = (lo[2] - o.z) * inv_d.z, t1z = (hi[2] - o.z) * inv_d.z;
+    const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
+    const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
+    return tnear <= tfar;
+}
+
+// ---------------------------------------------------------------------------------------------
+// traverse: plane triangles (Moller-Trumbore, back faces culled) then the LBVH.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void emit_candidate(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, const SceneDev& sc, uint32_t ray,
+                                               uint32_t prim) {
+    const uint32_t type = sc.prims[prim].type_id;
+    // warp-aggregated append: one atomic per (warp, type)
+    const unsigned peers = __match_any_sync(__activemask(), type);
+    const int leader = __ffs(peers) - 1;
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&ctrl->cand_count[type], (uint32_t)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    const uint32_t idx = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+    if (idx < pp.cand_capacity) wb.cand[type][idx] = make_uint2(ray, prim);
+    else ctrl->overflow = 1u;
+}
+
+template <bool PRIMARY>
+__global__ void __launch_bounds__(kBlock) k_traverse(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                     const __grid_constant__ WaveBuffers wb, int wave) {
+    WaveCtrl* ctrl = &wb.ctrl[wave];
+    const int pq = wave & 1;
+    const uint32_t n_rays = PRIMARY ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rays; r += gridDim.x * blockDim.x) {
+        V3 o, d;
+        uint32_t meta;
+        if (PRIMARY) {
+            const uint32_t px = pp.tile_x + r % pp.tile_w, py = pp.tile_y + r / pp.tile_w;
+            generate_camera_ray(px, py, pp.fc, o, d);
+            meta = make_meta(r, 1u, 0u);
+            wb.ray_o[pq][r] = make_float4(o.x, o.y, o.z, 0.0f);
+            wb.ray_d[pq][r] = make_float4(d.x, d.y, d.z, __uint_as_float(meta));
+        } else {
+            const float4 ro = wb.ray_o[pq][r], rd = wb.ray_d[pq][r];
+            o = ld3(ro); d = ld3(rd);
+            meta = __float_as_uint(rd.w);
+        }
+        const bool shadow = meta_shadow(meta) != 0u;
+        const float tmin = 0.0f;
+        float tcur = kRayTMax;
+        unsigned long long key = kKeyMiss;
+
+        // (i) triangle instance
+        if (sc.n_tris) {
+            const V3 oo = xform_point_3x4(sc.tri_w2o, o), dd = xform_vector_3x4(sc.tri_w2o, d);
+            for (uint32_t tri = 0; tri < sc.n_tris; tri++) {
+                const float* p = sc.tri_pos + 9 * tri;
+                const V3 v0 = v3(p[0], p[1], p[2]);
+                const V3 e1 = v3(p[3], p[4], p[5]) - v0, e2 = v3(p[6], p[7], p[8]) - v0;
+                const V3 pvec = cross(dd, e2);
+                const float det = dot(e1, pvec);
+                if (!(det > 0.0f)) continue; // clockwise = front; back faces culled
+                const float inv_det = 1.0f / det;
+                const V3 tvec = oo - v0;
+                const float u = dot(tvec, pvec) * inv_det;
+                if (u < 0.0f || u > 1.0f) continue;
+                const V3 qvec = cross(tvec, e1);
+                const float v = dot(dd, qvec) * inv_det;
+                if (v < 0.0f || u + v > 1.0f) continue;
+                const float t = dot(e2, qvec) * inv_det;
+                if (t > tmin && t < tcur) {
+                    tcur = t;
+                    key = pack_key(t, kCodePlane | tri);
+                    if (shadow) break;
+                }
+            }
+        }
+        wb.hitkey[r] = key;
+        wb.ray_tcur[r] = tcur;
+        if (shadow && key != kKeyMiss) continue; // ACCEPT_FIRST_HIT_AND_END_SEARCH
+        if (!sc.has_aabb_instance || sc.n_prims == 0) continue;
+
+        // (ii) procedural AABBs: every box whose slab test passes on [TMin, tcur] is a candidate
+        const V3 oo = xform_point_3x4(sc.aabb_w2o, o), dd = xform_vector_3x4(sc.aabb_w2o, d);
+        const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
+        if (pp.brute_force || sc.root_ref < 0) {
+            for (uint32_t i = 0; i < sc.n_prims; i++) {
+                const float* b = sc.aabbs + 6 * i;
+                if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) emit_candidate(pp, wb, ctrl, sc, r, i);
+            }
+        } else {
+            int32_t stack[64];
+            int sp = 0;
+            stack[sp++] = sc.root_ref;
+            while (sp) {
+                const int32_t node = stack[--sp];
+                const float4* n4 = sc.bvh_nodes + 4 * (size_t)node;
+                const float4 a = __ldg(n4), b = __ldg(n4 + 1), c = __ldg(n4 + 2), e = __ldg(n4 + 3);
+                const float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {a.w, b.x, b.y};
+                const float lo1[3] = {b.z, b.w, c.x}, hi1[3] = {c.y, c.z, c.w};
+                const int32_t ref0 = __float_as_int(e.x), ref1 = __float_as_int(e.y);
+                if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
+                    if (ref0 < 0) emit_candidate(pp, wb, ctrl, sc, r, (uint32_t)~ref0);
+                    else if (sp < 64) stack[sp++] = ref0;
+                }
+                if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
+                    if (ref1 < 0) emit_candidate(pp, wb, ctrl, sc, r, (uint32_t)~ref1);
+                    else if (sp < 64) stack[sp++] = ref1;
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// intersect<TYPE>: the intersection-shader body of one primitive type over its candidate queue
+// (MyIntersectionShader_* + GetRayInAABBPrimitiveLocalSpace, src/Raytracing.hlsl:277-341).
+// Persistent blocks pull chunks of the queue; its length is only known on the device.
+// ---------------------------------------------------------------------------------------------
+template <int TYPE, int NB>
+__device__ __forceinline__ bool run_test(const LocalRay& lr, const Material& mat, const PassParams& pp, float& thit, V3& n, uint32_t& work) {
+    if (TYPE == 0) { work++; return ray_unit_box(lr, thit, n); }
+    if (TYPE == 1) { work++; return ray_spheres(lr, thit, n); }
+    if (TYPE == 2) return ray_metaballs<NB>(lr, pp.fc.elapsed_time, pp.metaball_max_steps, thit, n, work);
+    return ray_sdf<(TYPE >= 3 ? TYPE - 3 : 0)>(lr, mat.step_scale, pp.sdf_max_steps, thit, n, work);
+}
+
+template <int TYPE, int NB>
+__global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                      const __grid_constant__ WaveBuffers wb, int wave) {
+    WaveCtrl* ctrl = &wb.ctrl[wave];
+    const int pq = wave & 1;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
+    __shared__ uint32_t s_base;
+    uint32_t work = 0;
+    for (;;) {
+        if (threadIdx.x == 0) s_base = atomicAdd(&ctrl->cursor[TYPE], (uint32_t)kBlock);
+        __syncthreads();
+        const uint32_t base = s_base;
+        __syncthreads();
+        if (base >= count) break;
+        const uint32_t c = base + threadIdx.x;
+        if (c >= count) continue;
+        const uint2 cand = wb.cand[TYPE][c];
+        const uint32_t r = cand.x, prim = cand.y;
+        const float4 rd = wb.ray_d[pq][r];
+        const uint32_t meta = __float_as_uint(rd.w);
+        float4 res = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        if (!(meta_shadow(meta) && wb.hitkey[r] != kKeyMiss)) { // shadow ray already occluded: skip
+            const float4 ro = wb.ray_o[pq][r];
+            const PrimRecord pr = sc.prims[prim];
+            const float* pf = sc.per_frame + 32 * (size_t)pr.instance_index;
+            const V3 oo = xform_point_3x4(sc.aabb_w2o, ld3(ro)), dd = xform_vector_3x4(sc.aabb_w2o, ld3(rd));
+            LocalRay lr;
+            lr.o = mul_point_rowvec(oo, pf + 16);
+            lr.d = mul_vector_rowvec(dd, pf + 16);
+            lr.tmin = 0.0f;
+            lr.tcur = wb.ray_tcur[r];
+            float thit = 0.0f;
+            V3 n = v3s(0.0f);
+            if (run_test<TYPE, NB>(lr, pr.mat, pp, thit, n, work) && thit >= lr.tmin && thit <= lr.tcur) {
+                // attr.normal = mul(n, (float3x3)local_to_blas); normalize(mul((float3x3)ObjectToWorld3x4(), attr.normal))
+                const V3 nb = mul_vector_rowvec(n, pf);
+                const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
+                atomicMin(&wb.hitkey[r], pack_key(thit, prim));
+                res = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
+            }
+        }
+        wb.cand_res[TYPE][c] = res;
+    }
+    // work statistics: one atomic per warp
+    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
+    if ((threadIdx.x & 31) == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
+}
+
+// ---------------------------------------------------------------------------------------------
+// resolve: the candidate whose (t, primitive) equals the ray's winning key publishes its normal.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_resolve(const __grid_constant__ PassParams pp, const __grid_constant__ WaveBuffers wb, int wave,
+                                                    uint32_t type_mask) {
+    const WaveCtrl* ctrl = &wb.ctrl[wave];
+    for (int type = 0; type < kNumTypes; type++) {
+        if (!((type_mask >> type) & 1u)) continue;
+        const uint32_t count = min(ctrl->cand_count[type], pp.cand_capacity);
+        for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < count; c += gridDim.x * blockDim.x) {
+            const float4 res = wb.cand_res[type][c];
+            if (res.w < 0.0f) continue;
+            const uint2 cand = wb.cand[type][c];
+            if (wb.hitkey[cand.x] == pack_key(res.w, cand.y)) wb.hit_n[cand.x] = res;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// shade_spawn: per ray of wave `wave`: record the hit for the final fold and emit the next
+// wave's rays -- the TraceRay calls inside MyClosestHitShader_* (src/Raytracing.hlsl:189-207,
+// 226-242) under the depth rule of TraceRadianceRay / TraceShadowRayAndReportIfHit (:89,:117).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_shade_spawn(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                        const __grid_constant__ WaveBuffers wb, int wave) {
+    WaveCtrl* ctrl = &wb.ctrl[wave];
+    WaveCtrl* next = &wb.ctrl[wave + 1];
+    const int pq = wave & 1, nq = pq ^ 1;
+    const uint32_t n_rays = (wave == 1) ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
+    const uint32_t n_round = (n_rays + 31u) & ~31u;
+    const int lane = threadIdx.x & 31;
+    uint32_t cnt_radiance = 0, cnt_shadow = 0;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_round; r += gridDim.x * blockDim.x) {
+        bool spawn_shadow = false, spawn_refl = false;
+        V3 hit_pos = v3s(0.0f), sdir = v3s(0.0f), rdir = v3s(0.0f);
+        uint32_t pixel = 0, level = 0;
+        if (r < n_rays) {
+            const float4 rd = wb.ray_d[pq][r];
+            const uint32_t meta = __float_as_uint(rd.w);
+            pixel = meta_pixel(meta);
+            level = meta_level(meta);
+            const unsigned long long key = wb.hitkey[r];
+            const size_t li = (size_t)(level - 1u) * pp.n_pixels + pixel;
+            if (meta_shadow(meta)) {
+                cnt_shadow++;
+                wb.lvl_shadow[li] = (key != kKeyMiss) ? 1 : 0;
+            } else {
+                cnt_radiance++;
+                const uint32_t code = (uint32_t)(key & 0xFFFFFFFFull);
+                wb.lvl_code[li] = (key == kKeyMiss) ? kCodeMiss : code;
+                if (key != kKeyMiss) {
+                    const float t = __uint_as_float((uint32_t)(key >> 32));
+                    const float4 ro = wb.ray_o[pq][r];
+                    const V3 o = ld3(ro), d = ld3(rd);
+                    V3 n;
+                    float refl;
+                    if (code & kCodePlane) {
+                        const float* tn = sc.tri_nrm + 3 * (code & ~kCodePlane);
+                        n = v3(tn[0], tn[1], tn[2]);
+                        refl = sc.plane_mat.reflectance_coefficient;
+                    } else {
+                        n = ld3(wb.hit_n[r]);
+                        refl = sc.prims[code].mat.reflectance_coefficient;
+                    }
+                    wb.lvl_o_t[li] = make_float4(o.x, o.y, o.z, t);
+                    wb.lvl_d[li] = make_float4(d.x, d.y, d.z, 0.0f);
+                    wb.lvl_n[li] = make_float4(n.x, n.y, n.z, 0.0f);
+                    if (level < pp.max_depth) {
+                        hit_pos = o + t * d; // HitWorldPosition()
+                        const V3 lp = v3(pp.fc.light_position[0], pp.fc.light_position[1], pp.fc.light_position[2]);
+                        sdir = normalize(lp - hit_pos);
+                        spawn_shadow = true;
+                        if (refl > 0.001f) { rdir = reflect(d, n); spawn_refl = true; }
+                    }
+                }
+            }
+        }
+        // ballot/popc compaction into the next wave's queue
+        const unsigned bs = __ballot_sync(kFull, spawn_shadow), br = __ballot_sync(kFull, spawn_refl);
+        const uint32_t total = (uint32_t)(__popc(bs) + __popc(br));
+        if (total) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&next->n_rays, total);
+            base = __shfl_sync(kFull, base, 0);
+            const unsigned lt = (1u << lane) - 1u;
+            if (spawn_shadow) {
+                const uint32_t s = base + (uint32_t)__popc(bs & lt);
+                if (s < pp.ray_capacity) {
+                    wb.ray_o[nq][s] = make_float4(hit_pos.x, hit_pos.y, hit_pos.z, 0.0f);
+                    wb.ray_d[nq][s] = make_float4(sdir.x, sdir.y, sdir.z, __uint_as_float(make_meta(pixel, level, 1u)));
+                }
+            }
+            if (spawn_refl) {
+                const uint32_t s = base + (uint32_t)__popc(bs) + (uint32_t)__popc(br & lt);
+                if (s < pp.ray_capacity) {
+                    wb.ray_o[nq][s] = make_float4(hit_pos.x, hit_pos.y, hit_pos.z, 0.0f);
+                    wb.ray_d[nq][s] = make_float4(rdir.x, rdir.y, rdir.z, __uint_as_float(make_meta(pixel, level + 1u, 0u)));
+                }
+            }
+        }
+    }
+    // ray statistics (one atomic per warp)
+    for (int off = 16; off; off >>= 1) {
+        cnt_radiance += __shfl_xor_sync(kFull, cnt_radiance, off);
+        cnt_shadow += __shfl_xor_sync(kFull, cnt_shadow, off);
+    }
+    if (lane == 0) {
+        if (cnt_radiance) atomicAdd(&ctrl->n_radiance, cnt_radiance);
+        if (cnt_shadow) atomicAdd(&ctrl->n_shadow, cnt_shadow);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// final_color: fold the per-level hit records back to front -- the order in which the recursive
+// closest-hit / miss shaders return -- and store R8G8B8A8_UNORM (src/Raytracing.hlsl:164).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                        const __grid_constant__ WaveBuffers wb, const __grid_constant__ OutputBuffers ob) {
+    for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < pp.n_pixels; pixel += gridDim.x * blockDim.x) {
+        const uint32_t tx = pixel % pp.tile_w, ty = pixel / pp.tile_w;
+        const uint32_t px = pp.tile_x + tx, py = pp.tile_y + ty;
+        V4 color = v4s(0.0f); // TraceRadianceRay beyond the depth limit returns 0 (src/Raytracing.hlsl:89-92)
+        for (int level = (int)pp.max_depth; level >= 1; level--) {
+            const size_t li = (size_t)(level - 1) * pp.n_pixels + pixel;
+            const uint32_t code = wb.lvl_code[li];
+            if (code == kCodeNone) continue;
+            if (code == kCodeMiss) { color = background_color(); continue; } // MyMissShader
+            const float4 ot = wb.lvl_o_t[li], dd = wb.lvl_d[li], nn = wb.lvl_n[li];
+            const bool is_tri = (code & kCodePlane) != 0u;
+            const Material mat = is_tri ? sc.plane_mat : sc.prims[code].mat;
+            const bool in_shadow = ((uint32_t)level < pp.max_depth) ? (wb.lvl_shadow[li] != 0) : false;
+            color = closest_hit_color(pp.fc, ld3(ot), ld3(dd), ot.w, ld3(nn), mat, in_shadow, color, is_tri, px, py);
+        }
+        const uint32_t ox = ob.out_x0 + tx, oy = ob.out_y0 + ty;
+        *reinterpret_cast<uint32_t*>(ob.rgba8 + (size_t)oy * ob.pitch + (size_t)ox * 4u) = pack_unorm8(color);
+        const size_t oi = (size_t)oy * ob.out_w + ox;
+        if (ob.rgba_f32) ob.rgba_f32[oi] = make_float4(color.x, color.y, color.z, color.w);
+        if (ob.hit_ids) {
+            const uint32_t code = wb.lvl_code[pixel];
+            ob.hit_ids[oi] = (code == kCodeMiss || code == kCodeNone) ? 0xFFFFFFFFu : (code & kCodePlane) ? (0x00000000u | (code & ~kCodePlane)) : (0x10000000u | code);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+int g_sm_count = 0;
+int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
+int grid_for(uint32_t n_items, int blocks_per_sm) {
+    const long long need = ((long long)n_items + kBlock - 1) / kBlock;
+    const long long cap = (long long)sm_count() * blocks_per_sm;
+    return (int)(need < 1 ? 1 : (need < cap ? need : cap));
+}
+
+int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
+    if (wave == 1) k_traverse<true><<<grid_for(upper, 8), kBlock, 0, s>>>(sc, pp, wb, wave);
+    else k_traverse<false><<<grid_for(upper, 8), kBlock, 0, s>>>(sc, pp, wb, wave);
+    return 1;
+}
+
+template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intersect<TYPE, NB>, kBlock, 0);
+    if (per_sm < 1) per_sm = 1;
+    k_intersect<TYPE, NB><<<sm_count() * per_sm, kBlock, 0, s>>>(sc, pp, wb, wave);
+}
+
+int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, int type_id, int metaballs, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (type_id) {
+    case 0: launch_intersect_t<0, 3>(sc, pp, wb, wave, s); break;
+    case 1: launch_intersect_t<1, 3>(sc, pp, wb, wave, s); break;
+    case 2:
+        if (metaballs == 5) launch_intersect_t<2, 5>(sc, pp, wb, wave, s);
+        else launch_intersect_t<2, 3>(sc, pp, wb, wave, s);
+        break;
+    case 3: launch_intersect_t<3, 3>(sc, pp, wb, wave, s); break;
+    case 4: launch_intersect_t<4, 3>(sc, pp, wb, wave, s); break;
+    case 5: launch_intersect_t<5, 3>(sc, pp, wb, wave, s); break;
+    case 6: launch_intersect_t<6, 3>(sc, pp, wb, wave, s); break;
+    case 7: launch_intersect_t<7, 3>(sc, pp, wb, wave, s); break;
+    case 8: launch_intersect_t<8, 3>(sc, pp, wb, wave, s); break;
+    case 9: launch_intersect_t<9, 3>(sc, pp, wb, wave, s); break;
+    default: return 0;
+    }
+    return 1;
+}
+
+int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
+    k_resolve<<<sm_count() * 4, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
+    return 1;
+}
+
+int launch_shade_spawn(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
+    const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
+    k_shade_spawn<<<grid_for(upper, 8), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, wave);
+    return 1;
+}
+
+int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, const OutputBuffers& ob, void* stream) {
+    k_final_color<<<grid_for(pp.n_pixels, 8), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
+    return 1;
+}
+
+} // namespace
+
+#if defined(GPRT_KERNELS_FAST)
+const KernelTable* kernels_fast() {
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_resolve, launch_shade_spawn, launch_final_color, "fast"};
+    return &t;
+}
+#else
+const KernelTable* kernels_parity() {
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_resolve, launch_shade_spawn, launch_final_color, "parity"};
+    return &t;
+}
+#endif
+
+} // namespace gprt

@@ -1,0 +1,322 @@
+// lbvh.cu -- hand-written LBVH builder over the procedural AABBs.
+//
+// Replaces what Renderer::build_acceleration_structures (src/Renderer.cpp:788-835) asks the
+// D3D12 driver for (BuildRaytracingAccelerationStructure on the AABB BLAS, :660,:722).  B200 has
+// no RT cores, so the structure is ours:
+//   1. scene bounds            block reduction + ordered-int atomics
+//   2. 30-bit Morton codes     of the AABB centroids
+//   3. LSD radix sort          4 passes x 8 bits, warp-private digit counters, stable
+//   4. Karras 2012             one thread per internal node, (code, index) keys so duplicates split
+//   5. bottom-up refit         second-arrival-continues, child boxes stored in the parent
+// Node layout (64 B, 4 x float4): child0 min.xyz max.xyz | child1 min.xyz max.xyz | ref0 ref1 - -
+// with ref >= 0 an internal node, ref < 0 a leaf (~primitive index).  One 64-byte fetch per visit
+// yields both child boxes.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "lbvh.h"
+
+namespace gprt {
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kWarpsPerBlock = kBlock / 32;
+constexpr int kKeysPerWarp = 32 * 16; // each warp owns a contiguous run of 512 keys
+constexpr unsigned kFull = 0xFFFFFFFFu;
+
+__device__ __forceinline__ uint32_t float_to_ordered(float f) {
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ordered_to_float(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u);
+}
+
+// bounds[0..2] = min (ordered), bounds[3..5] = max (ordered) of the centroids
+__global__ void k_bounds(const float* __restrict__ aabbs, uint32_t n, uint32_t* bounds) {
+    float lo[3] = {__builtin_inff(), __builtin_inff(), __builtin_inff()}, hi[3] = {-__builtin_inff(), -__builtin_inff(), -__builtin_inff()};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float* b = aabbs + 6 * (size_t)i;
+        for (int k = 0; k < 3; k++) {
+            const float c = 0.5f * (b[k] + b[k + 3]);
+            lo[k] = fminf(lo[k], c);
+            hi[k] = fmaxf(hi[k], c);
+        }
+    }
+    for (int k = 0; k < 3; k++) {
+        for (int off = 16; off; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(kFull, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(kFull, hi[k], off));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+        for (int k = 0; k < 3; k++) {
+            atomicMin(&bounds[k], float_to_ordered(lo[k]));
+            atomicMax(&bounds[3 + k], float_to_ordered(hi[k]));
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) { // 10 bits -> every third bit
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+__global__ void k_morton(const float* __restrict__ aabbs, uint32_t n, const uint32_t* __restrict__ bounds, uint32_t* keys, uint32_t* vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* b = aabbs + 6 * (size_t)i;
+    uint32_t q[3];
+    for (int k = 0; k < 3; k++) {
+        const float lo = ordered_to_float(bounds[k]), hi = ordered_to_float(bounds[3 + k]);
+        const float ext = hi - lo;
+        const float c = 0.5f * (b[k] + b[k + 3]);
+        float u = ext > 0.0f ? (c - lo) / ext : 0.0f;
+        u = fminf(fmaxf(u * 1024.0f, 0.0f), 1023.0f);
+        q[k] = (uint32_t)u;
+    }
+    keys[i] = (expand_bits10(q[0]) << 2) | (expand_bits10(q[1]) << 1) | expand_bits10(q[2]);
+    vals[i] = i;
+}
+
+// ---- radix sort: one pass = histogram, scan, scatter -----------------------------------------
+// Warp w (global id) owns keys [w*512, w*512+512).  hist is digit-major: hist[d * n_warps + w].
+__global__ void k_radix_hist(const uint32_t* __restrict__ keys, uint32_t n, int shift, uint32_t* hist, uint32_t n_warps) {
+    __shared__ uint32_t s_cnt[kWarpsPerBlock][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * kWarpsPerBlock + warp;
+    for (int d = lane; d < 256; d += 32) s_cnt[warp][d] = 0;
+    __syncwarp();
+    if (gw < n_warps) {
+        const uint32_t begin = gw * kKeysPerWarp;
+        for (int it = 0; it < kKeysPerWarp / 32; it++) {
+            const uint32_t i = begin + it * 32 + lane;
+            const bool valid = i < n;
+            const uint32_t d = valid ? ((keys[i] >> shift) & 255u) : 256u + lane; // invalid lanes never match
+            const unsigned peers = __match_any_sync(kFull, d);
+            if (valid && (__ffs(peers) - 1) == lane) s_cnt[warp][d] += __popc(peers);
+            __syncwarp();
+        }
+        for (int d = lane; d < 256; d += 32) hist[(size_t)d * n_warps + gw] = s_cnt[warp][d];
+    }
+}
+
+// exclusive scan of `m` counters by one block
+__global__ void k_scan_exclusive(uint32_t* data, uint32_t m) {
+    __shared__ uint32_t s_part[1024];
+    const uint32_t per = (m + blockDim.x - 1) / blockDim.x;
+    const uint32_t begin = threadIdx.x * per, end = min(begin + per, m);
+    uint32_t sum = 0;
+    for (uint32_t i = begin; i < end; i++) sum += data[i];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    for (uint32_t off = 1; off < blockDim.x; off <<= 1) { // Hillis-Steele inclusive
+        uint32_t v = 0;
+        if (threadIdx.x >= off) v = s_part[threadIdx.x - off];
+        __syncthreads();
+        s_part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = (threadIdx.x == 0) ? 0u : s_part[threadIdx.x - 1];
+    for (uint32_t i = begin; i < end; i++) {
+        const uint32_t v = data[i];
+        data[i] = run;
+        run += v;
+    }
+}
+
+__global__ void k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, uint32_t* keys_out,
+                                uint32_t* vals_out, uint32_t n, int shift, const uint32_t* __restrict__ hist, uint32_t n_warps) {
+    __shared__ uint32_t s_off[kWarpsPerBlock][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * kWarpsPerBlock + warp;
+    if (gw >= n_warps) return;
+    for (int d = lane; d < 256; d += 32) s_off[warp][d] = hist[(size_t)d * n_warps + gw];
+    __syncwarp();
+    const uint32_t begin = gw * kKeysPerWarp;
+    for (int it = 0; it < kKeysPerWarp / 32; it++) {
+        const uint32_t i = begin + it * 32 + lane;
+        const bool valid = i < n;
+        uint32_t key = 0, val = 0;
+        if (valid) { key = keys_in[i]; val = vals_in[i]; }
+        const uint32_t d = valid ? ((key >> shift) & 255u) : 256u + lane;
+        const unsigned peers = __match_any_sync(kFull, d);
+        uint32_t base = 0;
+        if (valid) base = s_off[warp][d];
+        __syncwarp();
+        if (valid && (__ffs(peers) - 1) == lane) s_off[warp][d] = base + __popc(peers);
+        __syncwarp();
+        if (valid) {
+            const uint32_t pos = base + __popc(peers & ((1u << lane) - 1u)); // stable inside the warp
+            keys_out[pos] = key;
+            vals_out[pos] = val;
+        }
+    }
+}
+
+// ---- Karras 2012 ------------------------------------------------------------------------------
+__device__ __forceinline__ int delta(const uint32_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint32_t a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clz(a ^ b);
+}
+
+// children[2*i], children[2*i+1]: refs (>= 0 internal, < 0 leaf: ~sorted position); parents for refit
+__global__ void k_karras(const uint32_t* __restrict__ keys, int n, int32_t* children, int32_t* parent_internal, int32_t* parent_leaf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int32_t left = (lo == gamma) ? ~gamma : gamma;
+    const int32_t right = (hi == gamma + 1) ? ~(gamma + 1) : (gamma + 1);
+    children[2 * i] = left;
+    children[2 * i + 1] = right;
+    if (left < 0) parent_leaf[~left] = i; else parent_internal[left] = i;
+    if (right < 0) parent_leaf[~right] = i; else parent_internal[right] = i;
+    if (i == 0) parent_internal[0] = -1;
+}
+
+// ---- refit --------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_child_box(int32_t ref, const float* aabbs, const uint32_t* sorted_prims, const float* node_boxes, float* lo, float* hi) {
+    if (ref < 0) {
+        const float* b = aabbs + 6 * (size_t)sorted_prims[~ref];
+        for (int k = 0; k < 3; k++) { lo[k] = b[k]; hi[k] = b[k + 3]; }
+    } else {
+        // written by another thread during this launch: bypass L1 (a neighbouring box may have
+        // pulled a stale copy of the line into this SM earlier)
+        const float* b = node_boxes + 6 * (size_t)ref;
+        for (int k = 0; k < 3; k++) { lo[k] = __ldcg(b + k); hi[k] = __ldcg(b + k + 3); }
+    }
+}
+
+__global__ void k_refit(const float* __restrict__ aabbs, const uint32_t* __restrict__ sorted_prims, int n, const int32_t* __restrict__ children,
+                        const int32_t* __restrict__ parent_internal, const int32_t* __restrict__ parent_leaf, uint32_t* flags, float* node_boxes,
+                        float4* nodes) {
+    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= n) return;
+    int node = parent_leaf[leaf];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[node], 1u) == 0u) return; // first arrival stops; the second sees both children done
+        __threadfence();
+        const int32_t r0 = children[2 * node], r1 = children[2 * node + 1];
+        float lo0[3], hi0[3], lo1[3], hi1[3];
+        load_child_box(r0, aabbs, sorted_prims, node_boxes, lo0, hi0);
+        load_child_box(r1, aabbs, sorted_prims, node_boxes, lo1, hi1);
+        float* nb = node_boxes + 6 * (size_t)node;
+        for (int k = 0; k < 3; k++) {
+            // volatile-ish publish: written before the fence + atomic of the next level
+            nb[k] = fminf(lo0[k], lo1[k]);
+            nb[k + 3] = fmaxf(hi0[k], hi1[k]);
+        }
+        // leaf refs in the final nodes name the ORIGINAL primitive index
+        const int32_t f0 = r0 < 0 ? ~(int32_t)sorted_prims[~r0] : r0;
+        const int32_t f1 = r1 < 0 ? ~(int32_t)sorted_prims[~r1] : r1;
+        float4* out = nodes + 4 * (size_t)node;
+        out[0] = make_float4(lo0[0], lo0[1], lo0[2], hi0[0]);
+        out[1] = make_float4(hi0[1], hi0[2], lo1[0], lo1[1]);
+        out[2] = make_float4(lo1[2], hi1[0], hi1[1], hi1[2]);
+        out[3] = make_float4(__int_as_float(f0), __int_as_float(f1), 0.0f, 0.0f);
+        node = parent_internal[node];
+    }
+}
+
+} // namespace
+
+size_t lbvh_scratch_bytes(uint32_t n) {
+    const size_t n_warps = (n + kKeysPerWarp - 1) / kKeysPerWarp;
+    size_t b = 0;
+    b += 8 * sizeof(uint32_t);                 // bounds
+    b += 4 * (size_t)n * sizeof(uint32_t);     // keys/vals ping-pong
+    b += 256 * n_warps * sizeof(uint32_t);     // radix histogram
+    b += 2 * (size_t)n * sizeof(int32_t);      // children
+    b += 2 * (size_t)n * sizeof(int32_t);      // parents
+    b += (size_t)n * sizeof(uint32_t);         // flags
+    b += 6 * (size_t)n * sizeof(float);        // node boxes
+    return b + 16 * 256; // every sub-allocation is rounded up to 256 bytes
+}
+
+int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    int launches = 0;
+    if (n == 0) { *root_ref = INT32_MIN; return 0; }
+    if (n == 1) { *root_ref = ~0; cudaMemsetAsync(d_sorted_prims, 0, sizeof(uint32_t), s); return 0; }
+    const uint32_t n_warps = (n + kKeysPerWarp - 1) / kKeysPerWarp;
+    char* p = (char*)d_scratch;
+    auto take = [&](size_t bytes) { char* q = p; p += (bytes + 255) & ~(size_t)255; return (void*)q; };
+    uint32_t* bounds = (uint32_t*)take(8 * sizeof(uint32_t));
+    uint32_t* keys_a = (uint32_t*)take((size_t)n * 4);
+    uint32_t* keys_b = (uint32_t*)take((size_t)n * 4);
+    uint32_t* vals_a = (uint32_t*)take((size_t)n * 4);
+    uint32_t* vals_b = (uint32_t*)take((size_t)n * 4);
+    uint32_t* hist = (uint32_t*)take(256 * (size_t)n_warps * 4);
+    int32_t* children = (int32_t*)take(2 * (size_t)n * 4);
+    int32_t* parent_internal = (int32_t*)take((size_t)n * 4);
+    int32_t* parent_leaf = (int32_t*)take((size_t)n * 4);
+    uint32_t* flags = (uint32_t*)take((size_t)n * 4);
+    float* node_boxes = (float*)take(6 * (size_t)n * 4);
+
+    const int grid_n = (int)((n + kBlock - 1) / kBlock);
+    // bounds: min slots start at all-ones, max slots at zero (ordered encoding)
+    cudaMemsetAsync(bounds, 0xFF, 3 * sizeof(uint32_t), s);
+    cudaMemsetAsync(bounds + 3, 0x00, 3 * sizeof(uint32_t), s);
+    k_bounds<<<grid_n < 1184 ? grid_n : 1184, kBlock, 0, s>>>(d_aabbs, n, bounds); launches++;
+    k_morton<<<grid_n, kBlock, 0, s>>>(d_aabbs, n, bounds, keys_a, vals_a); launches++;
+    const int grid_w = (int)((n_warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    uint32_t *ki = keys_a, *ko = keys_b, *vi = vals_a, *vo = vals_b;
+    for (int pass = 0; pass < 4; pass++) {
+        const int shift = 8 * pass;
+        k_radix_hist<<<grid_w, kBlock, 0, s>>>(ki, n, shift, hist, n_warps); launches++;
+        k_scan_exclusive<<<1, 1024, 0, s>>>(hist, 256u * n_warps); launches++;
+        k_radix_scatter<<<grid_w, kBlock, 0, s>>>(ki, vi, ko, vo, n, shift, hist, n_warps); launches++;
+        uint32_t* t = ki; ki = ko; ko = t;
+        t = vi; vi = vo; vo = t;
+    }
+    // after 4 passes the sorted data is back in keys_a / vals_a
+    cudaMemcpyAsync(d_sorted_prims, vi, (size_t)n * 4, cudaMemcpyDeviceToDevice, s);
+    k_karras<<<grid_n, kBlock, 0, s>>>(ki, (int)n, children, parent_internal, parent_leaf); launches++;
+    cudaMemsetAsync(flags, 0, (size_t)n * 4, s);
+    k_refit<<<grid_n, kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes); launches++;
+    *root_ref = 0;
+    return launches;
+}
+
+int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream_) {
+    // scratch layout must match lbvh_build (children / parents are reused)
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (n < 2) return 0;
+    const uint32_t n_warps = (n + kKeysPerWarp - 1) / kKeysPerWarp;
+    char* p = (char*)d_scratch;
+    auto take = [&](size_t bytes) { char* q = p; p += (bytes + 255) & ~(size_t)255; return (void*)q; };
+    take(8 * sizeof(uint32_t));
+    for (int i = 0; i < 4; i++) take((size_t)n * 4);
+    take(256 * (size_t)n_warps * 4);
+    int32_t* children = (int32_t*)take(2 * (size_t)n * 4);
+    int32_t* parent_internal = (int32_t*)take((size_t)n * 4);
+    int32_t* parent_leaf = (int32_t*)take((size_t)n * 4);
+    uint32_t* flags = (uint32_t*)take((size_t)n * 4);
+    float* node_boxes = (float*)take(6 * (size_t)n * 4);
+    cudaMemsetAsync(flags, 0, (size_t)n * 4, s);
+    k_refit<<<(int)((n + kBlock - 1) / kBlock), kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes);
+    return 1;
+}
+
+} // namespace gprt

@@ -1,0 +1,125 @@
+// wavefront.cuh -- data layout shared by the wavefront kernels (kernels.cu, compiled once per
+// math mode) and the host-side context (gprt_api.cu).
+//
+// The reference's DispatchRays runs one recursive shader invocation tree per pixel
+// (src/Raytracing.hlsl:154-165 and the TraceRay calls under it).  Here the tree is flattened into
+// `max_recursion_depth` WAVES.  Wave k holds the level-k radiance rays plus the level-(k-1)
+// shadow rays; for each wave:
+//   traverse      ray vs plane triangles, then LBVH walk -> (ray, primitive) candidates appended
+//                 to one queue per primitive type (warp-aggregated atomics)
+//   intersect<T>  one kernel per primitive type: the type's intersection test on every candidate,
+//                 64-bit atomicMin of (t, primitive) per ray
+//   resolve       the winning candidate of each ray publishes its normal
+//   shade_spawn   stores the level's hit record per pixel, emits the next wave's shadow and
+//                 reflection rays (ballot/popc compaction)
+// and one final kernel folds the per-level hit records back to front into the pixel colour
+// (exactly the order in which the recursive closest-hit shaders return).
+#pragma once
+#include <stdint.h>
+
+#include "shade.cuh"
+
+namespace gprt {
+
+constexpr int kNumTypes = 10; // 0 analytic AABB, 1 analytic spheres, 2 metaballs, 3..9 SDF types 0..6
+constexpr int kMaxDepth = 8;  // waves; the reference uses 3
+constexpr float kRayTMax = 10000.0f; // src/Raytracing.hlsl:99,126
+constexpr uint32_t kCodeMiss = 0xFFFFFFFFu;
+constexpr uint32_t kCodeNone = 0xFEFEFEFEu; // no ray traced at this level (memset pattern 0xFE)
+constexpr uint32_t kCodePlane = 0x80000000u; // | triangle index
+constexpr unsigned long long kKeyMiss = 0xFFFFFFFFFFFFFFFFull;
+
+// ray meta word: pixel (26 bits) | level (4 bits, 1-based) | kind (1 bit: 1 = shadow)
+constexpr uint32_t kMetaPixelMask = (1u << 26) - 1u;
+__host__ __device__ inline uint32_t make_meta(uint32_t pixel, uint32_t level, uint32_t shadow) { return pixel | (level << 26) | (shadow << 30); }
+__host__ __device__ inline uint32_t meta_pixel(uint32_t m) { return m & kMetaPixelMask; }
+__host__ __device__ inline uint32_t meta_level(uint32_t m) { return (m >> 26) & 15u; }
+__host__ __device__ inline uint32_t meta_shadow(uint32_t m) { return (m >> 30) & 1u; }
+
+struct PrimRecord { // per geometry index; 48 bytes
+    Material mat;            // 36 B
+    uint32_t type_id;        // 0..kNumTypes-1
+    uint32_t instance_index; // into the per-frame transform buffer
+    uint32_t _pad;
+};
+
+struct SceneDev {
+    const float4* bvh_nodes; // 4 x float4 per internal node: child0 min|max, child1 min|max, refs
+    int32_t root_ref;        // >= 0 internal node, < 0 leaf (~primitive), INT32_MIN: no primitives
+    uint32_t n_prims;
+    const float* aabbs;      // 6 floats per primitive (BLAS object space)
+    const PrimRecord* prims;
+    const float* per_frame;  // 32 floats per instance_index: local->BLAS 4x4, BLAS->local 4x4
+    const float* tri_pos;    // 9 floats per triangle: v0, v1, v2 (object space)
+    const float* tri_nrm;    // 3 floats per triangle: normal of the vertex indices[0] names
+    uint32_t n_tris;
+    uint32_t has_aabb_instance;
+    float tri_w2o[12];       // world -> triangle BLAS object space (3x4)
+    float aabb_w2o[12];      // world -> AABB BLAS object space
+    float aabb_o2w[12];      // ObjectToWorld3x4() of the AABB instance
+    Material plane_mat;
+};
+
+struct WaveCtrl { // one per wave, zeroed at the start of a pass
+    uint32_t n_rays;
+    uint32_t n_radiance, n_shadow;
+    uint32_t cand_count[kNumTypes];
+    uint32_t cursor[kNumTypes];
+    uint32_t resolve_cursor;
+    uint32_t overflow;
+    uint32_t work[kNumTypes];   // per type: analytic tests / metaball march steps / SDF distance evaluations
+    uint32_t work2[kNumTypes];  // per type: metaball in-radius (quintic) evaluations; 0 elsewhere
+    uint32_t _pad[1];
+};
+
+struct PassParams {
+    FrameConstants fc;
+    uint32_t tile_x, tile_y, tile_w, tile_h; // this pass's pixel rectangle (global coordinates)
+    uint32_t n_pixels;                       // tile_w * tile_h
+    uint32_t max_depth, metaball_max_steps, sdf_max_steps;
+    uint32_t ray_capacity;                   // 2 * n_pixels
+    uint32_t cand_capacity;                  // per type
+    uint32_t brute_force;
+};
+
+struct WaveBuffers {
+    float4* ray_o[2];  // ping-pong by wave parity: xyz origin
+    float4* ray_d[2];  // xyz direction, w = meta bits
+    float* ray_tcur;   // RayTCurrent() seen by the intersection tests (min(TMax, plane t))
+    unsigned long long* hitkey; // (float_bits(t) << 32) | code, atomicMin
+    float4* hit_n;     // world normal of the winning procedural hit
+    uint2* cand[kNumTypes];      // (ray slot, primitive)
+    float4* cand_res[kNumTypes]; // world normal xyz, w = t (or -1: no hit)
+    WaveCtrl* ctrl;    // [kMaxDepth + 1]
+    // per-level, per-pixel hit records: index (level - 1) * n_pixels + pixel
+    float4* lvl_o_t;   // ray origin xyz, committed t
+    float4* lvl_d;     // ray direction xyz
+    float4* lvl_n;     // world normal xyz
+    uint32_t* lvl_code;
+    uint8_t* lvl_shadow;
+};
+
+struct OutputBuffers {
+    uint8_t* rgba8;    // tile row y at rgba8 + y * pitch
+    size_t pitch;
+    uint32_t* hit_ids; // optional, tile-packed
+    float4* rgba_f32;  // optional, tile-packed
+    uint32_t out_x0, out_y0; // position of this pass inside the caller's tile
+    uint32_t out_w;          // width of the caller's tile (for the packed optional outputs)
+};
+
+// Launcher table exported by each compilation of kernels.cu.
+struct KernelTable {
+    // all launchers enqueue on `stream` and return the number of kernels launched
+    int (*traverse)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, void* stream);
+    int (*intersect)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, int type_id, int metaballs, void* stream);
+    int (*resolve)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, uint32_t type_mask, void* stream);
+    int (*shade_spawn)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, void* stream);
+    int (*final_color)(const SceneDev&, const PassParams&, const WaveBuffers&, const OutputBuffers&, void* stream);
+    const char* name;
+};
+
+const KernelTable* kernels_parity();
+const KernelTable* kernels_fast();
+
+} // namespace gprt

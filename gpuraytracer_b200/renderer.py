@@ -10,7 +10,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _capi
-from ._capi import Config, Counters, Rect, SceneView, Timing, check, lib
+from ._capi import Config, Counters, KernelProfile, Rect, SceneView, Timing, check, lib
 
 
 @dataclass
@@ -98,6 +98,16 @@ class Renderer:
         t = Timing()
         check(self._lib.gprt_last_timing(self.context, C.byref(t)), "last_timing")
         return t
+
+    def kernel_profile(self) -> KernelProfile:
+        p = KernelProfile()
+        check(self._lib.gprt_get_kernel_profile(self.context, C.byref(p)), "get_kernel_profile")
+        return p
+
+    def measure_fp32_peak(self) -> float:
+        v = C.c_float(0)
+        check(self._lib.gprt_measure_fp32_peak(self.context, C.byref(v)), "measure_fp32_peak")
+        return float(v.value)
 
     def launch_count(self) -> int:
         return int(self._lib.gprt_last_launch_count(self.context))

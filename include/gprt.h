@@ -132,7 +132,8 @@ typedef struct gprt_config {
 
 enum { GPRT_MATH_PARITY = 0, /* IEEE mul/add/div/sqrt, no FMA contraction */
        GPRT_MATH_FAST   = 1  /* FMA contraction + fast intrinsics (what DXIL `fast` allows) */ };
-enum { GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1u /* test every AABB instead of walking the LBVH */ };
+enum { GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1u, /* test every AABB instead of walking the LBVH */
+       GPRT_FLAG_PROFILE_KERNELS = 2u        /* CUDA events around every kernel (gprt_get_kernel_profile) */ };
 
 typedef struct gprt_rect { uint32_t x, y, w, h; } gprt_rect; /* pixel tile, (0,0) = top-left */
 
@@ -144,6 +145,17 @@ typedef struct gprt_counters {
     uint64_t bvh_node_visits;
     uint64_t queue_overflow; /* non-zero: a queue overflowed and the image is incomplete   */
 } gprt_counters;
+
+/* Per-kernel device time of the last dispatch (only with GPRT_FLAG_PROFILE_KERNELS) and the work
+ * each intersection kernel did (always counted). */
+enum { GPRT_K_TRAVERSE = 0, GPRT_K_INTERSECT0 = 1 /* + type id 0..9 */, GPRT_K_RESOLVE = 11, GPRT_K_SHADE_SPAWN = 12,
+       GPRT_K_FINAL = 13, GPRT_K_COUNT = 14 };
+typedef struct gprt_kernel_profile {
+    float    ms[GPRT_K_COUNT];
+    uint32_t launches[GPRT_K_COUNT];
+    uint64_t work[10];       /* per type id: analytic tests / metaball march steps / SDF distance evaluations */
+    uint64_t candidates[10]; /* per type id: intersection-shader invocations */
+} gprt_kernel_profile;
 
 typedef struct gprt_timing {
     float dispatch_ms;    /* CUDA events around the last gprt_dispatch only (== DX::GPUTimer) */
@@ -227,7 +239,11 @@ int gprt_dispatch_host(gprt_ctx* ctx, const gprt_scene_cb* scene,
 int gprt_sync(gprt_ctx* ctx);
 int gprt_get_counters(gprt_ctx* ctx, gprt_counters* out); /* of the last dispatch; syncs */
 int gprt_last_timing(gprt_ctx* ctx, gprt_timing* out);    /* syncs                        */
+int gprt_get_kernel_profile(gprt_ctx* ctx, gprt_kernel_profile* out); /* syncs */
 int gprt_last_cuda_error(gprt_ctx* ctx);
+/* FP32 FMA issue-rate microbenchmark (TFLOP/s, 2 flop per FMA) on the context's device: the
+ * measured denominator of the FP32 roofline.  Blocking; a few milliseconds. */
+int gprt_measure_fp32_peak(gprt_ctx* ctx, float* tflops_out);
 /* Use an existing CUDA stream (cudaStream_t as void*) for all work of this context. */
 int gprt_set_stream(gprt_ctx* ctx, void* cuda_stream);
 /* Number of kernels launched by the last dispatch (for bench.py's gpu_launches). */
