@@ -1,0 +1,375 @@
+#!/usr/bin/env python3
+"""bench.py -- the driver's benchmark contract for the DXR hot path (BASELINE.json metric:
+Mrays/s and 1080p frame ms, primary + shadow + reflection rays, recursion 3).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config ID]
+
+One "step" = one DispatchRays pass over one frame of the workload (config 2: the reference's full
+procedural scene, 1920x1080, depth 3; elapsed_time advances 1/60 s per step so every step has new
+per-frame transforms).  `value` = rays traced (radiance + shadow, counted on the device) per
+second with the scene resident in HBM and the output left in HBM; `e2e` = the same through the
+host-facing call (host scene constants in, host RGBA8 frame out, copies inside the timed region).
+N > 1: one process per GPU (torchrun), the frame is sharded by interleaved row stripes, every rank
+renders its stripes and rank 0 gathers the RGBA8 rows over NCCL (strong scaling: total work fixed).
+`--impl reference` times the reference's own shader code on the host cores (oracle/_ref).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "mrays_per_s"
+UNIT = "Mrays/s (radiance + shadow rays)"
+
+CONFIGS = {
+    1: {"scene_id": 1, "workload": "config1: analytic sphere cluster + ground quad, 640x480, depth 2 (primary + shadow)"},
+    2: {"scene_id": 2, "workload": "config2: full reference procedural scene, 1920x1080, recursion 3"},
+    3: {"scene_id": 3, "workload": "config3: SDF/fractal-heavy 4x4 grid, 3840x2160, recursion 3"},
+    4: {"scene_id": 4, "workload": "config4: 3x3 metaball AABBs with 5 animated metaballs, 1920x1080, recursion 3"},
+    5: {"scene_id": 5, "workload": "config5: 1000x1000 instanced AABB grid (1M primitives), 7680x4320, recursion 3"},
+}
+
+# Algorithmic FP32 work per counted unit (FMA = 2, everything else = 1),
+# per kernel type id: analytic box / spheres per test, metaball per march step (3 balls outside
+# their radius + position update), SDF per distance evaluation incl. the 9-flop march overhead.
+FLOPS_PER_UNIT = [30 + 42, 3 * 35 + 42, 3 * 11 + 6, 48 + 9, 34 + 9, 16 + 9, 20 + 9, 71 + 9, 66 + 9, 228 + 9]
+KNAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
+          "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final"]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        for row in self.rows:
+            f = [x.strip() for x in row.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax = float(f[1])
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        # median of the upper half: the samples taken while kernels were running
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def stripe_rows_for(height, n):
+    """Largest stripe height <= 8 such that every rank gets the same number of whole stripes."""
+    if n == 1:
+        return height
+    for s in (8, 6, 5, 4, 3, 2, 1):
+        if height % (s * n) == 0:
+            return s
+    return 1
+
+
+def run_gpu(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from gpuraytracer_b200 import GPRT_MATH_FAST, GPRT_MATH_PARITY, Renderer, default_config
+    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    conf = CONFIGS[args.config]
+    cfg = default_config()
+    cfg.math_mode = GPRT_MATH_PARITY if args.math == "parity" else GPRT_MATH_FAST
+    cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0  # the scene's own
+    r = Renderer(scene_id=conf["scene_id"], device=local_rank, config=cfg)
+    r.on_init()
+    W, H = r.width, r.height
+    stream = torch.cuda.current_stream()
+    r.set_stream(stream.cuda_stream)
+
+    srows = stripe_rows_for(H, world)
+    local_rows = H // world if world > 1 else H
+    frame_local = torch.empty((local_rows, W, 4), dtype=torch.uint8, device=dev)
+    gathered = [torch.empty_like(frame_local) for _ in range(world)] if (world > 1 and rank == 0) else None
+    frame_full = torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else frame_local
+    host_frame = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def frame(step, to_host):
+        """One step: update (host), dispatch, [gather], [D2H]."""
+        r.on_update(step / 60.0)
+        if world == 1:
+            if to_host:
+                r.on_render(out=host_frame.numpy())  # host in, host out through gprt_dispatch_host
+            else:
+                r.do_raytracing(frame_local.data_ptr())
+            return
+        r.do_raytracing_striped(frame_local.data_ptr(), srows, rank, world)
+        dist.gather(frame_local, gathered, dst=0)
+        if rank == 0:
+            # un-interleave: rank k owns stripes k, k+world, ...
+            full = frame_full.view(H // (srows * world), world, srows, W, 4)
+            for k in range(world):
+                full[:, k].copy_(gathered[k].view(H // (srows * world), srows, W, 4))
+            if to_host:
+                host_frame.copy_(frame_full, non_blocking=True)
+                stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(steps, first_step, to_host):
+        """Sum of per-step device intervals (CUDA events on the launching stream), L2 flushed before each."""
+        total_ms, rays = 0.0, 0
+        barrier()
+        wall0 = time.perf_counter()
+        for i in range(steps):
+            flush.zero_()
+            if world > 1:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record(stream)
+            frame(first_step + i, to_host)
+            e1.record(stream)
+            e1.synchronize()
+            host_ms = (time.perf_counter() - t0) * 1e3
+            ms = max(e0.elapsed_time(e1), host_ms) if to_host else e0.elapsed_time(e1)
+            if world > 1:
+                t = torch.tensor([ms], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            total_ms += ms
+            c = r.counters()
+            rays += int(c.radiance_rays) + int(c.shadow_rays)
+        barrier()
+        wall = time.perf_counter() - wall0
+        if world > 1:
+            t = torch.tensor([rays], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            rays = int(t.item())
+        return total_ms, rays, wall
+
+    for i in range(args.warmup):
+        frame(i, False)
+        frame(i, True)
+    barrier()
+    launches_per_step = r.launch_count()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    dev_ms, dev_rays, dev_wall = timed(args.steps, args.warmup, False)
+    e2e_ms, e2e_rays, _ = timed(args.steps, args.warmup, True)
+    clocks = sampler.stop() if rank == 0 else None
+
+    result = None
+    if rank == 0:
+        value = dev_rays / (dev_ms * 1e-3) / 1e6
+        result = {
+            "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": conf["workload"], "width": W, "height": H, "math_mode": args.math, "l2_flush": "256 MiB memset before every timed step",
+                       "timing": "sum of per-step CUDA-event intervals on the launching stream, max over ranks",
+                       "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, {srows}-row stripes interleaved, NCCL gather to rank 0"},
+            "primary_mrays_per_s": round(W * H * args.steps / (dev_ms * 1e-3) / 1e6, 3),
+            "rays_per_step": dev_rays // args.steps,
+            "e2e": {"value": round(e2e_rays / (e2e_ms * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "h2d_bytes_per_step": 136 + 128 * len(r.scene().per_frame), "d2h_bytes_per_step": W * H * 4},
+            "gpu_launches": launches_per_step * args.steps * 2,
+            "clocks": clocks,
+        }
+    if rank == 0:
+        result["roofline"], result["roofline_hbm"], result["kernel_ms"] = roofline(args, conf, local_rank, cfg, world)
+        if world == 1:
+            result["cpu_baseline"] = cpu_baseline(conf, steps=2)
+    r.on_destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return result
+
+
+def roofline(args, conf, device, cfg, world):
+    """Per-kernel device times (CUDA events around every launch, on the launching stream) of full
+    single-GPU frames of the same workload; the dominant kernel's algorithmic FP32 work / time
+    against the measured FFMA peak, and the most memory-bound kernel's bytes / time against the
+    measured HBM copy bandwidth."""
+    from gpuraytracer_b200 import Renderer
+    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS
+    cfg.flags = GPRT_FLAG_PROFILE_KERNELS
+    with Renderer(scene_id=conf["scene_id"], device=device, config=cfg) as r:
+        r.on_init()
+        W, H = r.width, r.height
+        ms = [0.0] * 14
+        work = [0] * 10
+        launches = [0] * 14
+        reps = 5
+        for i in range(2 + reps):
+            r.on_update((args.warmup + i) / 60.0)
+            r.on_render()
+            if i < 2:
+                continue
+            p = r.kernel_profile()
+            for k in range(14):
+                ms[k] += p.ms[k]
+                launches[k] += p.launches[k]
+            for t in range(10):
+                work[t] += p.work[t]
+        c = r.counters()
+        rays = int(c.radiance_rays) + int(c.shadow_rays)
+        fp32_peak = r.measure_fp32_peak()
+    cfg.flags = 0
+    ms = [m / reps for m in ms]
+    work = [w / reps for w in work]
+    launches = [n // reps for n in launches]
+    kernel_ms = {KNAMES[k]: round(ms[k], 4) for k in range(14) if launches[k]}
+    # dominant kernel among the intersection kernels (type ids 0..9 -> kernel kinds 1..10)
+    dom = max(range(10), key=lambda t: ms[1 + t])
+    flops = work[dom] * FLOPS_PER_UNIT[dom]
+    dur = ms[1 + dom] * 1e-3
+    n_l = max(launches[1 + dom], 1)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    achieved = flops / dur / 1e12 if dur > 0 else 0.0
+    peak_src = "measured in this run: FFMA issue-rate probe (gprt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure"
+    if not fp32_peak or fp32_peak <= 0:
+        fp32_peak, peak_src = 74.4, "nominal fallback: 148 SMs x 128 lanes x 2 x 1.965 GHz"
+    roof = {"bound": "fp32", "kernel": KNAMES[1 + dom], "achieved": round(achieved, 3), "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
+            "frac": round(achieved / fp32_peak, 4), "traffic": None, "peak_source": peak_src,
+            "flops_per_launch": flops / n_l, "units_per_launch": work[dom] / n_l, "flops_per_unit": FLOPS_PER_UNIT[dom],
+            "launches_per_step": n_l, "avg_launch_ms": round(ms[1 + dom] / n_l, 4),
+            "note": "not a tensor-core path: the march kernels are FP32-issue bound (SURVEY.md 8d)"}
+    # memory-bound kernel: final fold = per pixel, per existing level 53 B of hit record read + 4 B written
+    levels = rays  # one hit record per radiance ray ~ radiance rays; bounded above by all rays
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    fin_bytes = W * H * (4 + 3 * 4) + int(c.radiance_rays) * 49
+    fin_dur = ms[13] * 1e-3
+    hbm = {"bound": "hbm", "kernel": "final", "achieved": round(fin_bytes / fin_dur / 1e9, 1) if fin_dur > 0 else 0.0, "peak": hbm_peak,
+           "unit": "GB/s", "frac": round(fin_bytes / fin_dur / 1e9 / hbm_peak, 4) if fin_dur > 0 else 0.0, "traffic": None,
+           "peak_source": hbm_src, "bytes_per_launch": fin_bytes}
+    return roof, hbm, kernel_ms
+
+
+def oracle_for(conf, fast=True):
+    from gpuraytracer_b200 import Renderer
+    from oracle import oracle
+    r = Renderer(scene_id=conf["scene_id"], device=None)
+    scene = r.scene()
+    mb = scene.config.metaballs_count
+    orc = oracle.load(metaballs=mb, fast=fast) if oracle.available("reference", mb, fast) else oracle.load(metaballs=mb)
+    return r, orc
+
+
+def cpu_frames(conf, steps, first_step=0, tile_rows=None):
+    """Time `steps` frames (or row bands) of the workload on the host cores with the oracle."""
+    r, orc = oracle_for(conf)
+    total_s, rays, pixels = 0.0, 0, 0
+    for i in range(steps):
+        r.on_update((first_step + i) / 60.0)
+        scene = r.scene()
+        orc.set_scene(scene)
+        tile = None if tile_rows is None else (0, (scene.height - tile_rows) // 2, scene.width, tile_rows)
+        t0 = time.perf_counter()
+        res = orc.render(scene, tile=tile, want_ids=False)
+        total_s += time.perf_counter() - t0
+        rays += res["counters"]["radiance_rays"] + res["counters"]["shadow_rays"]
+        pixels += (scene.width * (tile_rows or scene.height))
+    return total_s, rays, pixels, orc
+
+
+def cpu_baseline(conf, steps=2):
+    total_s, rays, pixels, orc = cpu_frames(conf, steps)
+    return {"value": round(rays / total_s / 1e6, 3), "unit": UNIT, "cores": orc.max_threads(), "kind": orc.kind,
+            "sample": f"{steps} full frames of the same workload ({pixels} pixels), OpenMP over rows, {os.path.basename(orc.path)}",
+            "ms_per_step": round(total_s / steps * 1e3, 2)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    conf = CONFIGS[args.config]
+    for _ in range(min(args.warmup, 1)):
+        cpu_frames(conf, 1)
+    total_s, rays, pixels, orc = cpu_frames(conf, args.steps, first_step=args.warmup)
+    value = rays / total_s / 1e6
+    return {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(total_s / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": conf["workload"]},
+            "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": orc.max_threads(), "kind": orc.kind,
+                             "sample": f"{args.steps} full frames ({pixels} pixels), OpenMP over rows, {os.path.basename(orc.path)}"},
+            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="gprt", choices=["gprt", "reference"])
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--math", default=os.environ.get("GPRT_BENCH_MATH", "parity"), choices=["parity", "fast"])
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "gprt":
+        args.warmup = 3
+    res = run_reference(args) if args.impl == "reference" else run_gpu(args)
+    if res is not None:
+        print(json.dumps(res), flush=True)
+
+
+if __name__ == "__main__":
+    main()

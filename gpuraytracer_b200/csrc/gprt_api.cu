@@ -90,6 +90,7 @@ struct gprt_ctx {
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_used = 0;
     std::vector<Interval> intervals;
+    bool per_type_launches = false; // GPRT_PER_TYPE_LAUNCHES=1: one intersect launch per type (A/B aid)
 };
 
 namespace {
@@ -309,11 +310,15 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     int launches = 0;
     for (uint32_t wave = 1; wave <= D; wave++) {
         { ScopedInterval si(c, GPRT_K_TRAVERSE); launches += c->kt->traverse(c->scene, pp, c->wb, (int)wave, c->stream); }
-        for (int t = 0; t < kNumTypes; t++)
-            if ((c->type_mask >> t) & 1u) {
-                ScopedInterval si(c, GPRT_K_INTERSECT0 + t);
-                launches += c->kt_isect->intersect(c->scene, pp, c->wb, (int)wave, t, (int)c->cfg.metaballs_count, c->stream);
-            }
+        if ((c->cfg.flags & GPRT_FLAG_PROFILE_KERNELS) || c->per_type_launches) {
+            for (int t = 0; t < kNumTypes; t++)
+                if ((c->type_mask >> t) & 1u) {
+                    ScopedInterval si(c, GPRT_K_INTERSECT0 + t);
+                    launches += c->kt_isect->intersect(c->scene, pp, c->wb, (int)wave, t, (int)c->cfg.metaballs_count, c->stream);
+                }
+        } else if (c->type_mask) {
+            launches += c->kt_isect->intersect_all(c->scene, pp, c->wb, (int)wave, c->type_mask, (int)c->cfg.metaballs_count, c->stream);
+        }
         if (c->type_mask) { ScopedInterval si(c, GPRT_K_RESOLVE); launches += c->kt->resolve(c->scene, pp, c->wb, (int)wave, c->type_mask, c->stream); }
         { ScopedInterval si(c, GPRT_K_SHADE_SPAWN); launches += c->kt->shade_spawn(c->scene, pp, c->wb, (int)wave, c->stream); }
     }
@@ -363,6 +368,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     // lines) do not survive approximate division.
     c->kt = kernels_parity();
     c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : kernels_parity();
+    { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
     std::memset(&c->scene, 0, sizeof c->scene);
     std::memset(&c->wb, 0, sizeof c->wb);
     std::memset(c->h_instances, 0, sizeof c->h_instances);

@@ -5,6 +5,8 @@
 // file:line each piece follows.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "prims.cuh"
 #include "wavefront.cuh"
 
@@ -341,6 +343,14 @@ __global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ 
     }
 }
 
+} // namespace
+} // namespace gprt
+
+#include "march.cuh" // k_march_sdf / k_march_metaballs (same anonymous namespace)
+
+namespace gprt {
+namespace {
+
 // ---------------------------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------------------------
@@ -368,11 +378,33 @@ int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers&
     return 1;
 }
 
-template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
+// GPRT_SIMPLE_ISECT=1 selects the one-candidate-per-thread kernels for every type (A/B aid).
+bool simple_isect() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("GPRT_SIMPLE_ISECT"); v = (e && e[0] == '1') ? 1 : 0; }
+    return v == 1;
+}
+
+template <class K> int persistent_grid(K kernel) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intersect<TYPE, NB>, kBlock, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0);
     if (per_sm < 1) per_sm = 1;
-    k_intersect<TYPE, NB><<<sm_count() * per_sm, kBlock, 0, s>>>(sc, pp, wb, wave);
+    return sm_count() * per_sm;
+}
+
+template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
+    if (TYPE >= 2 && !simple_isect()) {
+        if (TYPE == 2) {
+            static const int grid = persistent_grid(k_march_metaballs<NB>);
+            k_march_metaballs<NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+        } else {
+            static const int grid = persistent_grid(k_march_sdf<(TYPE >= 3 ? TYPE - 3 : 0)>);
+            k_march_sdf<(TYPE >= 3 ? TYPE - 3 : 0)><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+        }
+        return;
+    }
+    static const int grid = persistent_grid(k_intersect<TYPE, NB>);
+    k_intersect<TYPE, NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
 }
 
 int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, int type_id, int metaballs, void* stream) {
@@ -396,6 +428,31 @@ int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers
     return 1;
 }
 
+// GPRT_ISECT_VARIANT: 0 = lane-to-completion, N > 0 = marchers refilling once N lanes idle (A/B aid)
+int isect_variant() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 0; }
+    return v;
+}
+template <int NB, int RMIN> void launch_all_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
+    static const int grid = persistent_grid(k_intersect_all<NB, RMIN>);
+    k_intersect_all<NB, RMIN><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
+}
+template <int NB> void launch_all_v(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
+    switch (isect_variant()) {
+    case 1: launch_all_t<NB, 1>(sc, pp, wb, wave, type_mask, s); break;
+    case 8: launch_all_t<NB, 8>(sc, pp, wb, wave, type_mask, s); break;
+    case 16: launch_all_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
+    case 24: launch_all_t<NB, 24>(sc, pp, wb, wave, type_mask, s); break;
+    default: launch_all_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
+    }
+}
+int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {
+    if (metaballs == 5) launch_all_v<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+    else launch_all_v<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+    return 1;
+}
+
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
     k_resolve<<<sm_count() * 4, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
     return 1;
@@ -416,12 +473,12 @@ int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffe
 
 #if defined(GPRT_KERNELS_FAST)
 const KernelTable* kernels_fast() {
-    static const KernelTable t = {launch_traverse, launch_intersect, launch_resolve, launch_shade_spawn, launch_final_color, "fast"};
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "fast"};
     return &t;
 }
 #else
 const KernelTable* kernels_parity() {
-    static const KernelTable t = {launch_traverse, launch_intersect, launch_resolve, launch_shade_spawn, launch_final_color, "parity"};
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "parity"};
     return &t;
 }
 #endif
