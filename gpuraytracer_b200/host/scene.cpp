@@ -315,7 +315,7 @@ bool build_scene(SceneState& s, int scene_id, uint32_t width, uint32_t height, u
                 s.primitives.push_back(from_template(tt, initialize_aabb(base, stride, (float)ix, 0, (float)iz, size)));
             }
         set_plane(s, (uint32_t)(n * 1.4) + 1, (uint32_t)(n * 1.4) + 1, -0.5f);
-        eye[1] = 60.0; eye[2] = -170.0;
+        eye[1] = 25.0; eye[2] = -50.0; // fog (exp(-2e-6 t^3)) hides everything beyond t ~ 125
         time0 = 1.0f;
         break;
     }

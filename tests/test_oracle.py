@@ -1,0 +1,161 @@
+"""CPU tests that pin the oracle: function-level known answers, the committed golden images
+(tests/golden, generated from the reference-compiled oracle), DXR-semantics properties."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from gpuraytracer_b200 import Renderer
+from oracle import oracle
+from tests.golden.make_golden import FIXTURES, HERE as GOLDEN_DIR, render_fixture
+
+AX_O, AX_D = (0.0, 0.0, -5.0), (0.0, 0.0, 1.0)
+
+
+def test_oracle_kind_and_threads(oracle3, oracle5):
+    assert oracle3.kind in ("reference", "port") and oracle3.metaballs == 3 and oracle5.metaballs == 5
+    assert oracle3.max_threads() >= 1
+
+
+# Known answers of single intersection tests along the local -z axis (SURVEY.md Appendix E.2,
+# re-derived here): (hit group kind, type, step scale) -> (hit, t, normal)
+@pytest.mark.parametrize("kind,typ,expect_t,expect_n", [
+    (1, 0, 4.0, (0, 0, -1)),             # analytic AABB: front face of [-1,1]^3
+    (3, 2, 4.1, (0, 0, -1)),             # SquareTorus: 0.75 + 0.15 box-ish ring
+    (3, 4, 4.1, (0, 0, -1)),             # Cog
+])
+def test_axis_ray_hits(oracle3, kind, typ, expect_t, expect_n):
+    hit, t, n = oracle3.intersect_local(kind, typ, AX_O, AX_D)
+    assert hit and abs(t - expect_t) < 2e-4
+    np.testing.assert_allclose(n, expect_n, atol=2e-3)
+
+
+def test_axis_ray_spheres_and_pyramid_and_metaballs(oracle3):
+    hit, t, n = oracle3.intersect_local(1, 1, AX_O, AX_D)   # Spheres: the r=0.6 sphere at (-0.3,-0.3,-0.3)
+    assert hit and abs(t - 4.275735) < 1e-4
+    np.testing.assert_allclose(n, (0.5, 0.5, -0.7071), atol=1e-3)
+    hit, t, n = oracle3.intersect_local(3, 6, AX_O, AX_D, step_scale=0.8)  # FractalPyramid
+    assert hit and abs(t - 4.49994) < 1e-3 and n[2] < -0.9
+    hit, t, n = oracle3.intersect_local(2, 0, AX_O, AX_D, elapsed_time=0.0)  # Metaballs
+    assert hit and abs(t - 5.218956) < 1e-3
+    np.testing.assert_allclose(n, (0, 0.580, -0.815), atol=5e-3)
+
+
+@pytest.mark.parametrize("typ", [0, 1, 3, 5])
+def test_axis_ray_misses(oracle3, typ):
+    # MiniSpheres, IntersectedRoundCube, TwistedTorus, Cylinder: the axis passes through the cut-outs
+    assert not oracle3.intersect_local(3, typ, AX_O, AX_D, step_scale=0.5 if typ == 3 else 1.0)[0]
+
+
+def test_back_face_culling_and_interval(oracle3):
+    # from inside the unit box every face is back-facing: no hit (IsCulled in local space)
+    assert not oracle3.intersect_local(1, 0, (0, 0, 0), (0, 0, 1))[0]
+    # closed interval: a hit exactly at RayTCurrent is accepted, beyond it rejected
+    assert oracle3.intersect_local(1, 0, AX_O, AX_D, tcurrent=4.0)[0]
+    assert not oracle3.intersect_local(1, 0, AX_O, AX_D, tcurrent=3.999)[0]
+    # un-normalised direction: t scales, the hit point does not
+    hit, t, _ = oracle3.intersect_local(1, 0, AX_O, (0, 0, 2.0))
+    assert hit and abs(t - 2.0) < 1e-6
+
+
+def test_scalar_helpers(oracle3):
+    assert oracle3.checkers((0.3, 0.7), (0.01, 0), (0, 0.01), 50) == pytest.approx(1.0)
+    assert oracle3.checkers((0.005, 0.5), (0.001, 0), (0, 0.001), 50) < 0.5   # on a grid line
+    np.testing.assert_allclose(oracle3.fresnel((0, 0, 1), (0, 0, -1), (0.5, 0.5, 0.5)), 0.5, atol=1e-6)
+    np.testing.assert_allclose(oracle3.fresnel((1, 0, 0), (0, 0, -1), (0.5, 0.5, 0.5)), 1.0, atol=1e-6)  # grazing
+    # 12 s ping-pong smoothstep (CalculateAnimationInterpolant)
+    assert oracle3.animation_interpolant(0.0, 12.0) == 0.0
+    assert oracle3.animation_interpolant(6.0, 12.0) == pytest.approx(1.0)
+    assert oracle3.animation_interpolant(3.0, 12.0) == pytest.approx(0.5)
+    assert oracle3.animation_interpolant(15.0, 12.0) == pytest.approx(oracle3.animation_interpolant(3.0, 12.0))
+    # SDF values: sphere-ish distances at the origin / far away
+    assert oracle3.sdf_distance(2, (0, 0, 0)) == pytest.approx(0.6, abs=1e-5)       # SquareTorus: 0.75 - 0.15
+    assert oracle3.sdf_distance(6, (0, 5.0, 0)) > 1.0                                # above the pyramid
+
+
+def test_camera_ray_centre_pixel_looks_at_origin():
+    s = Renderer(scene_id=0, width=641, height=361, device=None).scene()
+    orc = oracle.load(metaballs=3)
+    o, d = orc.camera_ray(s, 320, 180)
+    np.testing.assert_allclose(o, s.scene_cb[0]["camera_position"][:3])
+    np.testing.assert_allclose(d, -o / np.linalg.norm(o), atol=1e-4)  # the unprojected point sits 0.01 from the eye
+
+
+@pytest.mark.parametrize("name", sorted(FIXTURES))
+def test_golden_images(name):
+    """The oracle reproduces the committed golden vectors bit for bit."""
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "golden_meta.json")))[name]
+    _, res = render_fixture(name)
+    if oracle.load(metaballs=3).kind == "reference":
+        np.testing.assert_array_equal(res["rgba8"], g["rgba8"])
+        np.testing.assert_array_equal(res["hit_ids"], g["hit_ids"])
+        assert res["counters"]["radiance_rays"] == meta["counters"]["radiance_rays"]
+        assert res["counters"]["shadow_rays"] == meta["counters"]["shadow_rays"]
+    else:  # the port may differ from the reference build in the last bit of a transcendental
+        assert np.abs(res["rgba8"].astype(int) - g["rgba8"].astype(int)).max(axis=-1).__gt__(2).mean() <= 1e-3
+        assert (res["hit_ids"] != g["hit_ids"]).mean() <= 2e-3
+
+
+def test_reference_image_statistics():
+    """Qualitative pin: the frame is the Microsoft procedural-geometry picture (pyramid in the
+    centre, sky on top, every primitive visible)."""
+    g = np.load(os.path.join(GOLDEN_DIR, "ref_scene_t0.npz"))
+    ids = g["hit_ids"]
+    assert set(np.unique(ids).tolist()) >= {0xFFFFFFFF, 0x00000000, *(0x10000000 | i for i in range(10))}
+    assert (ids[:3] == 0xFFFFFFFF).all()                       # sky above the pyramid's apex
+    assert ids[72 // 3, 128 // 2] == (0x10000000 | 9)         # the fractal pyramid
+    np.testing.assert_array_equal(g["rgba8"][0, 0, :3], [204, 230, 255])  # BACKGROUND_COLOR (0.8, 0.9, 1.0)
+
+
+def test_depth_rule_and_ray_counts():
+    """MAX_RAY_RECURSION_DEPTH rule (src/Raytracing.hlsl:89,117): config 1 (depth 2, nothing
+    reflective) traces one shadow ray per primary hit and no reflection rays."""
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "golden_meta.json")))
+    g = np.load(os.path.join(GOLDEN_DIR, "config1.npz"))
+    c = meta["config1"]["counters"]
+    assert c["radiance_rays"] == g["hit_ids"].size
+    assert c["shadow_rays"] == int((g["hit_ids"] != 0xFFFFFFFF).sum())
+    c = meta["ref_scene_t0"]["counters"]
+    rays_per_pixel = (c["radiance_rays"] + c["shadow_rays"]) / (128 * 72)
+    assert 2.6 < rays_per_pixel < 2.9   # 2.76
+
+
+def test_depth_one_traces_no_secondary_rays(oracle3):
+    s = Renderer(scene_id=0, width=64, height=36, device=None).scene()
+    oracle3.set_scene(s, max_recursion_depth=1)
+    c = oracle3.render(s)["counters"]
+    assert c["radiance_rays"] == 64 * 36 and c["shadow_rays"] == 0
+
+
+def test_host_bvh_equals_brute_force(oracle3):
+    """> 64 primitives switch the oracle to its host BVH: same candidate set, same image."""
+    s = Renderer(scene_id=5, width=96, height=54, grid_n=12, device=None).scene()
+    assert len(s.aabbs) == 144
+    oracle3.set_scene(s)
+    a = oracle3.render(s)
+    oracle3.set_scene(s, force_brute_force=True)
+    b = oracle3.render(s)
+    np.testing.assert_array_equal(a["rgba8"], b["rgba8"])
+    np.testing.assert_array_equal(a["hit_ids"], b["hit_ids"])
+    assert a["counters"]["aabb_tests"] < b["counters"]["aabb_tests"]
+    assert a["counters"]["isect"] == b["counters"]["isect"]
+
+
+def test_tile_render_equals_full_frame(oracle3):
+    s = Renderer(scene_id=0, width=96, height=54, device=None).scene()
+    oracle3.set_scene(s)
+    full = oracle3.render(s)
+    tile = oracle3.render(s, tile=(32, 20, 40, 16))
+    np.testing.assert_array_equal(tile["rgba8"], full["rgba8"][20:36, 32:72])
+    np.testing.assert_array_equal(tile["hit_ids"], full["hit_ids"][20:36, 32:72])
+
+
+def test_thread_count_does_not_change_the_image(oracle3):
+    s = Renderer(scene_id=0, width=64, height=36, device=None).scene()
+    oracle3.set_scene(s)
+    a = oracle3.render(s, threads=1)
+    b = oracle3.render(s, threads=4)
+    np.testing.assert_array_equal(a["rgba8"], b["rgba8"])
+    assert a["counters"] == b["counters"]
