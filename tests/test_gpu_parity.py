@@ -1,0 +1,272 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libgprt.so via ctypes), against the
+CPU oracle on identical scene constants.  Acceptance (BASELINE.json north_star): >= 99.9 % of the
+pixels within 2/255 per channel, primary hit ids equal away from silhouettes."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from gpuraytracer_b200 import GPRT_FLAG_BRUTE_FORCE_TRAVERSAL, GPRT_MATH_FAST, GPRT_MATH_PARITY, GprtError, Renderer, _capi, default_config
+from oracle import oracle
+from tests.golden.make_golden import FIXTURES, HERE as GOLDEN_DIR
+from tests.parity import MAX_MISMATCH, report
+
+pytestmark = pytest.mark.gpu
+
+
+def make_cfg(math_mode=GPRT_MATH_PARITY, flags=0):
+    cfg = default_config()
+    cfg.math_mode = math_mode
+    cfg.flags = flags
+    cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0  # keep the scene's own
+    return cfg
+
+
+def gpu_render(scene_id, w, h, t=0.0, grid_n=0, tile=None, math_mode=GPRT_MATH_PARITY, flags=0):
+    with Renderer(scene_id=scene_id, width=w, height=h, grid_n=grid_n, device=0, config=make_cfg(math_mode, flags)) as r:
+        r.on_init()
+        r.on_update(t)
+        img, ids = r.on_render(tile=tile, want_hit_ids=True)
+        return img, ids, r.scene(), r.counters(), r.launch_count()
+
+
+def oracle_render(scene, tile=None):
+    orc = oracle.load(metaballs=scene.config.metaballs_count)
+    orc.set_scene(scene)
+    return orc.render(scene, tile=tile)
+
+
+def check(ref, img, ids, max_mismatch=MAX_MISMATCH, id_slack=0):
+    rep = report(ref["rgba8"], img, ref["hit_ids"], ids)
+    assert rep["mismatch_frac_gt2"] <= max_mismatch, rep
+    assert rep["id_mismatch_interior"] <= id_slack, rep
+    return rep
+
+
+@pytest.mark.parametrize("name", sorted(FIXTURES))
+def test_against_golden_fixtures(name):
+    """CUDA path vs the committed golden vectors (generated from the reference-compiled oracle)."""
+    scene_id, w, h, grid_n, t, tile = FIXTURES[name]
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    img, ids, _, c, launches = gpu_render(scene_id, w, h, t, grid_n, tile)
+    assert launches > 0
+    rep = report(g["rgba8"], img, g["hit_ids"], ids)
+    # small images: allow 3 pixels beyond the 0.1 % rule
+    assert (rep["mismatch_frac_gt2"] * img.shape[0] * img.shape[1]) <= max(3, MAX_MISMATCH * img.size / 4), rep
+    assert rep["id_mismatch_interior"] == 0, rep
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "golden_meta.json")))[name]["counters"]
+    assert abs(int(c.radiance_rays) - meta["radiance_rays"]) <= 2 + meta["radiance_rays"] // 2000
+    assert abs(int(c.shadow_rays) - meta["shadow_rays"]) <= 2 + meta["shadow_rays"] // 2000
+
+
+@pytest.mark.parametrize("t", [0.0, 0.9, 3.0])
+def test_reference_scene_parity(t):
+    img, ids, scene, c, _ = gpu_render(0, 640, 360, t)
+    ref = oracle_render(scene)
+    check(ref, img, ids)
+    # the ray tree is the same: identical counts up to the handful of pixels that differ
+    assert abs(int(c.radiance_rays) - ref["counters"]["radiance_rays"]) <= 20
+    assert abs(int(c.shadow_rays) - ref["counters"]["shadow_rays"]) <= 20
+
+
+def test_reference_scene_fast_math_mode():
+    img, ids, scene, _, _ = gpu_render(0, 640, 360, 0.4, math_mode=GPRT_MATH_FAST)
+    check(oracle_render(scene), img, ids, id_slack=2)
+
+
+def test_config1_primary_and_shadow_only():
+    img, ids, scene, c, _ = gpu_render(1, 640, 480)
+    ref = oracle_render(scene)
+    check(ref, img, ids)
+    assert int(c.radiance_rays) == 640 * 480
+    assert int(c.shadow_rays) == int((ids != 0xFFFFFFFF).sum())
+
+
+def test_config2_full_size_1080p():
+    """BASELINE config 2 at its full size against the oracle (about 0.5 s of CPU)."""
+    img, ids, scene, c, _ = gpu_render(2, 0, 0, 0.25)
+    assert img.shape == (1080, 1920, 4)
+    ref = oracle_render(scene)
+    check(ref, img, ids)
+    assert abs(int(c.radiance_rays) + int(c.shadow_rays) - ref["counters"]["radiance_rays"] - ref["counters"]["shadow_rays"]) <= 100
+
+
+def test_config3_sdf_heavy():
+    img, ids, scene, _, _ = gpu_render(3, 480, 270)
+    check(oracle_render(scene), img, ids)
+
+
+def test_config3_long_march_budget():
+    img, ids, scene, _, _ = gpu_render(6, 320, 180)
+    assert scene.config.sdf_max_steps == 2048
+    check(oracle_render(scene), img, ids)
+
+
+@pytest.mark.parametrize("k", [0, 3, 7, 12])
+def test_config4_five_metaballs_time_sweep(k):
+    img, ids, scene, _, _ = gpu_render(4, 480, 270, 0.75 * k)
+    assert scene.config.metaballs_count == 5
+    check(oracle_render(scene), img, ids)
+
+
+def test_config5_lbvh_equals_brute_force_and_oracle():
+    """LBVH traversal must produce exactly the brute-force candidate set (bit-identical images)."""
+    a_img, a_ids, scene, a_c, _ = gpu_render(5, 480, 270, 1.0, grid_n=32)
+    b_img, b_ids, _, b_c, _ = gpu_render(5, 480, 270, 1.0, grid_n=32, flags=GPRT_FLAG_BRUTE_FORCE_TRAVERSAL)
+    np.testing.assert_array_equal(a_img, b_img)
+    np.testing.assert_array_equal(a_ids, b_ids)
+    assert list(a_c.candidates) == list(b_c.candidates)
+    check(oracle_render(scene), a_img, a_ids)
+
+
+def test_config5_million_primitives_tile():
+    """BASELINE config 5 at full scale (1000 x 1000 grid, 7680 x 4320 dispatch): one tile, LBVH vs
+    brute force bit-identical, and parity against the oracle (host BVH) on the same tile."""
+    tile = (3520, 2200, 640, 160)  # one grid cell spans ~480 px at 8K near the image centre
+    a_img, a_ids, scene, _, _ = gpu_render(5, 0, 0, 1.0, tile=tile)
+    assert len(scene.aabbs) == 1_000_000 and (scene.width, scene.height) == (7680, 4320)
+    b_img, b_ids, _, _, _ = gpu_render(5, 0, 0, 1.0, tile=tile, flags=GPRT_FLAG_BRUTE_FORCE_TRAVERSAL)
+    np.testing.assert_array_equal(a_img, b_img)
+    np.testing.assert_array_equal(a_ids, b_ids)
+    ref = oracle_render(scene, tile=tile)
+    rep = report(ref["rgba8"], a_img, ref["hit_ids"], a_ids)
+    assert rep["mismatch_frac_gt2"] <= MAX_MISMATCH, rep
+    assert rep["id_mismatch_interior"] == 0, rep
+    assert ((a_ids & 0xF0000000) == 0x10000000).any() and (a_ids == 0).any()
+
+
+def test_tiles_compose_to_the_full_frame():
+    """Tile dispatches (DispatchRaysIndex stays global) are bit-identical to the full dispatch."""
+    full, full_ids, _, _, _ = gpu_render(0, 320, 180, 0.3)
+    for tile in [(0, 0, 160, 90), (160, 90, 160, 90), (37, 11, 201, 53)]:
+        img, ids, _, _, _ = gpu_render(0, 320, 180, 0.3, tile=tile)
+        x, y, w, h = tile
+        np.testing.assert_array_equal(img, full[y:y + h, x:x + w])
+        np.testing.assert_array_equal(ids, full_ids[y:y + h, x:x + w])
+
+
+def test_deterministic_and_reusable_context():
+    with Renderer(scene_id=0, width=320, height=180, device=0, config=make_cfg()) as r:
+        r.on_init()
+        r.on_update(0.7)
+        a, _ = r.on_render()
+        a = a.copy()
+        r.on_update(1.9)
+        r.on_render()
+        r.on_update(0.7)
+        b, _ = r.on_render()
+        np.testing.assert_array_equal(a, b)
+        r.on_size_changed(256, 144)
+        c, _ = r.on_render()
+        assert c.shape == (144, 256, 4)
+        t = r.timing()
+        assert t.dispatch_ms > 0 and t.build_accel_ms > 0
+        assert r.primary_mrays_per_s() > 0
+
+
+def test_internal_banding_is_invisible():
+    """A frame larger than the internal pass size is rendered in bands; compare against tiles."""
+    with Renderer(scene_id=0, width=2560, height=1800, device=0, config=make_cfg()) as r:  # 4.6 Mpx > 2^22
+        r.on_init()
+        full, _ = r.on_render()
+        tile, _ = r.on_render(tile=(1000, 1500, 400, 200))
+        np.testing.assert_array_equal(tile, full[1500:1700, 1000:1400])
+
+
+def test_device_output_and_optional_buffers():
+    import torch
+    with Renderer(scene_id=0, width=320, height=180, device=0, config=make_cfg()) as r:
+        r.on_init()
+        r.set_stream(torch.cuda.current_stream().cuda_stream)
+        img = torch.zeros((180, 320, 4), dtype=torch.uint8, device="cuda")
+        ids = torch.zeros((180, 320), dtype=torch.int32, device="cuda")
+        f32 = torch.zeros((180, 320, 4), dtype=torch.float32, device="cuda")
+        r.do_raytracing(img.data_ptr(), d_hit_ids_ptr=ids.data_ptr(), d_rgba_f32_ptr=f32.data_ptr())
+        r.sync()
+        host, host_ids = r.on_render(want_hit_ids=True)
+        np.testing.assert_array_equal(img.cpu().numpy(), host)
+        np.testing.assert_array_equal(ids.cpu().numpy().view(np.uint32), host_ids)
+        f = f32.cpu().numpy()
+        q = np.floor(np.clip(np.nan_to_num(f), 0, 1) * 255 + 0.5).astype(np.uint8)
+        np.testing.assert_array_equal(q, host)  # the UNORM store of the UAV
+
+
+def test_depth_parameter():
+    for depth, expect_shadow in ((1, False), (2, True), (4, True)):
+        cfg = make_cfg()
+        cfg.max_recursion_depth = depth
+        with Renderer(scene_id=0, width=160, height=90, device=0, config=cfg) as r:
+            r.on_init()
+            img, ids = r.on_render(want_hit_ids=True)
+            scene, c = r.scene(), r.counters()
+        assert (int(c.shadow_rays) > 0) == expect_shadow
+        orc = oracle.load(metaballs=3)
+        orc.set_scene(scene, max_recursion_depth=depth)
+        ref = orc.render(scene)
+        rep = report(ref["rgba8"], img, ref["hit_ids"], ids)
+        assert rep["mismatch_frac_gt2"] * 160 * 90 <= 15, rep
+        assert int(c.radiance_rays) == pytest.approx(ref["counters"]["radiance_rays"], abs=5)
+
+
+def test_error_behaviour_on_device():
+    import ctypes as C
+    lib = _capi.lib()
+    h = C.c_void_p()
+    cfg = default_config()
+    assert lib.gprt_create(C.byref(h), 0, C.byref(cfg)) == 0
+    assert lib.gprt_build_accel(h) == _capi.GPRT_E_INVALID_ARG       # no geometry yet
+    buf = (C.c_uint8 * 1024)()
+    cb = np.zeros(1, _capi.SCENE_CB_DTYPE)
+    rc = lib.gprt_dispatch_host(h, cb.ctypes.data, None, 0, 16, 16, _capi.Rect(0, 0, 16, 16), buf, 64, None)
+    assert rc == _capi.GPRT_E_NOT_BUILT
+    assert lib.gprt_create(C.byref(C.c_void_p()), 99, C.byref(cfg)) == _capi.GPRT_E_NO_DEVICE
+    lib.gprt_destroy(h)
+    with Renderer(scene_id=0, width=64, height=36, device=0, config=make_cfg()) as r:
+        r.on_init()
+        with pytest.raises(GprtError):
+            r.on_render(tile=(60, 30, 16, 16))                       # tile outside the dispatch
+
+
+def test_empty_and_degenerate_scenes():
+    """No procedural primitives at all / a single one (LBVH root is a leaf)."""
+    import ctypes as C
+    lib = _capi.lib()
+    s = Renderer(scene_id=1, width=96, height=72, device=None).scene()
+    for n_prims in (0, 1):
+        h = C.c_void_p()
+        cfg = default_config()
+        cfg.max_recursion_depth = 2
+        assert lib.gprt_create(C.byref(h), 0, C.byref(cfg)) == 0
+        aabbs = np.ascontiguousarray(s.aabbs[:n_prims])
+        hg = np.ascontiguousarray(s.hit_groups[:2 + 2 * n_prims])
+        assert lib.gprt_set_geometry(h, aabbs.ctypes.data, n_prims, s.vertices.ctypes.data, 4, s.indices.ctypes.data, 6,
+                                     s.instances.ctypes.data, 2) == 0
+        assert lib.gprt_set_hit_group_table(h, hg.ctypes.data, len(hg), 96) == 0
+        assert lib.gprt_build_accel(h) == 0
+        img = np.zeros((72, 96, 4), np.uint8)
+        ids = np.zeros((72, 96), np.uint32)
+        pf = np.ascontiguousarray(s.per_frame[:max(n_prims, 1)])
+        assert lib.gprt_dispatch_host(h, s.scene_cb.ctypes.data, pf.ctypes.data, len(pf), 96, 72, _capi.Rect(0, 0, 96, 72),
+                                      img.ctypes.data, 96 * 4, ids.ctypes.data) == 0
+        lib.gprt_destroy(h)
+        present = set(np.unique(ids).tolist())
+        assert 0xFFFFFFFF in present and (0 in present or 1 in present)
+        assert ((0x10000000 in present) == (n_prims == 1))
+    g = np.load(os.path.join(GOLDEN_DIR, "config1.npz"))
+    assert (np.abs(img.astype(int) - g["rgba8"].astype(int)).max(-1) > 2).sum() <= 3
+
+
+def test_refit_accel_matches_rebuild():
+    import ctypes as C
+    lib = _capi.lib()
+    with Renderer(scene_id=5, width=320, height=180, grid_n=16, device=0, config=make_cfg()) as r:
+        r.on_init()
+        s = r.scene()
+        moved = s.aabbs.copy()
+        moved["min"][:, 1] += 0.0  # same boxes: refit must reproduce the image exactly
+        a, _ = r.on_render()
+        a = a.copy()
+        assert lib.gprt_refit_accel(r.context, moved.ctypes.data, len(moved)) == 0
+        b, _ = r.on_render()
+        np.testing.assert_array_equal(a, b)
