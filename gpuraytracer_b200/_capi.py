@@ -45,6 +45,11 @@ class KernelProfile(C.Structure):
     _fields_ = [("ms", C.c_float * 14), ("launches", C.c_uint32 * 14), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
 
 
+class WaveStats(C.Structure):
+    _fields_ = [("n_radiance", C.c_uint32), ("n_shadow", C.c_uint32), ("candidates", C.c_uint32 * 10), ("work", C.c_uint32 * 10),
+                ("max_evals", C.c_uint32 * 10), ("evals_hist", (C.c_uint32 * 12) * 10)]
+
+
 class Timing(C.Structure):
     _fields_ = [("dispatch_ms", C.c_float), ("build_accel_ms", C.c_float)]
 
@@ -101,6 +106,7 @@ def lib():
         "gprt_last_timing": (i32, [vp, C.POINTER(Timing)]),
         "gprt_get_kernel_profile": (i32, [vp, C.POINTER(KernelProfile)]),
         "gprt_measure_fp32_peak": (i32, [vp, C.POINTER(C.c_float)]),
+        "gprt_get_wave_stats": (i32, [vp, u32, C.POINTER(WaveStats)]),
         "gprt_last_cuda_error": (i32, [vp]),
         "gprt_set_stream": (i32, [vp, vp]),
         "gprt_last_launch_count": (i32, [vp]),
@@ -129,7 +135,7 @@ def lib():
 EXPORTED_SYMBOLS = [
     "gprt_default_config", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
     "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_host", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
-    "gprt_get_kernel_profile", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
+    "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
     "gprt_renderer_do_raytracing", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",

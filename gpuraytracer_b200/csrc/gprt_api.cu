@@ -352,6 +352,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     if (c0.max_recursion_depth < 1 || c0.max_recursion_depth > (uint32_t)kMaxDepth) return GPRT_E_UNSUPPORTED;
     if (c0.metaballs_count != 3 && c0.metaballs_count != 5) return GPRT_E_UNSUPPORTED;
     if (c0.metaball_max_steps == 0 || c0.sdf_max_steps == 0) return GPRT_E_INVALID_ARG;
+    if (c0.metaball_max_steps > 0xFFFFu) return GPRT_E_UNSUPPORTED; // the pool marcher packs the step count in 16 bits
     if (c0.math_mode != GPRT_MATH_PARITY && c0.math_mode != GPRT_MATH_FAST) return GPRT_E_INVALID_ARG;
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
@@ -613,6 +614,23 @@ int gprt_get_kernel_profile(gprt_ctx* c, gprt_kernel_profile* out) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
             for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += wc.cand_count[t]; }
         }
+    return GPRT_OK;
+}
+
+int gprt_get_wave_stats(gprt_ctx* c, uint32_t wave, gprt_wave_stats* out) {
+    if (!c || !out || wave < 1 || wave > (uint32_t)kMaxDepth) return GPRT_E_INVALID_ARG;
+    std::memset(out, 0, sizeof *out);
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->n_bands_last < 1 || wave > c->last_depth) return GPRT_OK;
+    const WaveCtrl& wc = c->h_ctrl[0].ctrl[wave];
+    out->n_radiance = wc.n_radiance;
+    out->n_shadow = wc.n_shadow;
+    for (int t = 0; t < kNumTypes; t++) {
+        out->candidates[t] = wc.cand_count[t];
+        out->work[t] = wc.work[t];
+        out->max_evals[t] = wc.max_evals[t];
+        for (int b = 0; b < 12; b++) out->evals_hist[t][b] = wc.evals_hist[t][b];
+    }
     return GPRT_OK;
 }
 

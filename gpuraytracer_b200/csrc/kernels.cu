@@ -184,7 +184,14 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
             lr.tcur = wb.ray_tcur[r];
             float thit = 0.0f;
             V3 n = v3s(0.0f);
-            if (run_test<TYPE, NB>(lr, pr.mat, pp, thit, n, work) && thit >= lr.tmin && thit <= lr.tcur) {
+            const uint32_t work0 = work;
+            const bool hit = run_test<TYPE, NB>(lr, pr.mat, pp, thit, n, work);
+            { // per-candidate cost statistics (this one-candidate-per-thread kernel is the profiling path)
+                const uint32_t dw = work - work0;
+                atomicMax(&ctrl->max_evals[TYPE], dw);
+                atomicAdd(&ctrl->evals_hist[TYPE][dw ? min(11, 32 - __clz(dw)) : 0], 1u);
+            }
+            if (hit && thit >= lr.tmin && thit <= lr.tcur) {
                 // attr.normal = mul(n, (float3x3)local_to_blas); normalize(mul((float3x3)ObjectToWorld3x4(), attr.normal))
                 const V3 nb = mul_vector_rowvec(n, pf);
                 const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
@@ -347,6 +354,7 @@ __global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ 
 } // namespace gprt
 
 #include "march.cuh" // k_march_sdf / k_march_metaballs (same anonymous namespace)
+#include "march_coop.cuh" // k_intersect_coop: warp-cooperative sphere tracer (the production path)
 
 namespace gprt {
 namespace {
@@ -378,11 +386,13 @@ int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers&
     return 1;
 }
 
-// GPRT_SIMPLE_ISECT=1 selects the one-candidate-per-thread kernels for every type (A/B aid).
-bool simple_isect() {
-    static int v = -1;
-    if (v < 0) { const char* e = getenv("GPRT_SIMPLE_ISECT"); v = (e && e[0] == '1') ? 1 : 0; }
-    return v == 1;
+// GPRT_ISECT_VARIANT (A/B aid): unset or 200+R = warp-cooperative marchers refilling once R lanes idle
+// (the production path, R = 8); -1 = one candidate per lane to completion; 16 = per-lane state
+// machines with refill (march.cuh).
+int isect_variant() {
+    static int v = -1000;
+    if (v == -1000) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 208; }
+    return v;
 }
 
 template <class K> int persistent_grid(K kernel) {
@@ -393,7 +403,14 @@ template <class K> int persistent_grid(K kernel) {
 }
 
 template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
-    if (TYPE >= 2 && !simple_isect()) {
+    if constexpr (TYPE >= 3) {
+        if (isect_variant() >= 200) {
+            static const int grid = persistent_grid(k_coop_sdf<TYPE - 3, 8>);
+            k_coop_sdf<TYPE - 3, 8><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+            return;
+        }
+    }
+    if (TYPE >= 2 && isect_variant() > 0) {
         if (TYPE == 2) {
             static const int grid = persistent_grid(k_march_metaballs<NB>);
             k_march_metaballs<NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
@@ -428,23 +445,21 @@ int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers
     return 1;
 }
 
-// GPRT_ISECT_VARIANT: 0 = lane-to-completion, N > 0 = marchers refilling once N lanes idle (A/B aid)
-int isect_variant() {
-    static int v = -1;
-    if (v < 0) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 0; }
-    return v;
-}
 template <int NB, int RMIN> void launch_all_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
     static const int grid = persistent_grid(k_intersect_all<NB, RMIN>);
     k_intersect_all<NB, RMIN><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
+template <int NB, int RMIN> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
+    static const int grid = persistent_grid(k_intersect_coop<NB, RMIN>);
+    k_intersect_coop<NB, RMIN><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
+}
 template <int NB> void launch_all_v(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
     switch (isect_variant()) {
-    case 1: launch_all_t<NB, 1>(sc, pp, wb, wave, type_mask, s); break;
-    case 8: launch_all_t<NB, 8>(sc, pp, wb, wave, type_mask, s); break;
+    case -1: launch_all_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
     case 16: launch_all_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
-    case 24: launch_all_t<NB, 24>(sc, pp, wb, wave, type_mask, s); break;
-    default: launch_all_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
+    case 201: launch_coop_t<NB, 1>(sc, pp, wb, wave, type_mask, s); break;
+    case 216: launch_coop_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
+    default: launch_coop_t<NB, 8>(sc, pp, wb, wave, type_mask, s); break;
     }
 }
 int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {

@@ -68,7 +68,8 @@ struct WaveCtrl { // one per wave, zeroed at the start of a pass
     uint32_t resolve_cursor;
     uint32_t overflow;
     uint32_t work[kNumTypes];   // per type: analytic tests / metaball march steps / SDF distance evaluations
-    uint32_t work2[kNumTypes];  // per type: metaball in-radius (quintic) evaluations; 0 elsewhere
+    uint32_t max_evals[kNumTypes];      // profiling: most field evaluations spent on one candidate
+    uint32_t evals_hist[kNumTypes][12]; // profiling: candidates by floor(log2(evaluations)) (bin 0: none)
     uint32_t _pad[1];
 };
 

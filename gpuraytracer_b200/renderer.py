@@ -10,7 +10,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _capi
-from ._capi import Config, Counters, KernelProfile, Rect, SceneView, Timing, check, lib
+from ._capi import Config, Counters, KernelProfile, Rect, SceneView, Timing, WaveStats, check, lib
 
 
 @dataclass
@@ -103,6 +103,11 @@ class Renderer:
         p = KernelProfile()
         check(self._lib.gprt_get_kernel_profile(self.context, C.byref(p)), "get_kernel_profile")
         return p
+
+    def wave_stats(self, wave) -> WaveStats:
+        w = WaveStats()
+        check(self._lib.gprt_get_wave_stats(self.context, int(wave), C.byref(w)), "get_wave_stats")
+        return w
 
     def measure_fp32_peak(self) -> float:
         v = C.c_float(0)

@@ -157,6 +157,17 @@ typedef struct gprt_kernel_profile {
     uint64_t candidates[10]; /* per type id: intersection-shader invocations */
 } gprt_kernel_profile;
 
+/* Per-wave statistics of the last dispatch (wave k = level-k radiance rays + level-(k-1) shadow
+ * rays).  max_evals / evals_hist are filled by the one-candidate-per-thread intersection kernels
+ * only (GPRT_FLAG_PROFILE_KERNELS with GPRT_ISECT_VARIANT=-1). */
+typedef struct gprt_wave_stats {
+    uint32_t n_radiance, n_shadow;
+    uint32_t candidates[10];
+    uint32_t work[10];
+    uint32_t max_evals[10];
+    uint32_t evals_hist[10][12]; /* candidates by floor(log2(field evaluations)) + 1; bin 0 = none */
+} gprt_wave_stats;
+
 typedef struct gprt_timing {
     float dispatch_ms;    /* CUDA events around the last gprt_dispatch only (== DX::GPUTimer) */
     float build_accel_ms; /* last gprt_build_accel                                            */
@@ -240,6 +251,7 @@ int gprt_sync(gprt_ctx* ctx);
 int gprt_get_counters(gprt_ctx* ctx, gprt_counters* out); /* of the last dispatch; syncs */
 int gprt_last_timing(gprt_ctx* ctx, gprt_timing* out);    /* syncs                        */
 int gprt_get_kernel_profile(gprt_ctx* ctx, gprt_kernel_profile* out); /* syncs */
+int gprt_get_wave_stats(gprt_ctx* ctx, uint32_t wave, gprt_wave_stats* out); /* wave 1..depth; first band; syncs */
 int gprt_last_cuda_error(gprt_ctx* ctx);
 /* FP32 FMA issue-rate microbenchmark (TFLOP/s, 2 flop per FMA) on the context's device: the
  * measured denominator of the FP32 roofline.  Blocking; a few milliseconds. */
