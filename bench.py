@@ -39,8 +39,6 @@ CONFIGS = {
 # per kernel type id: analytic box / spheres per test, metaball per march step (3 balls outside
 # their radius + position update), SDF per distance evaluation incl. the 9-flop march overhead.
 FLOPS_PER_UNIT = [30 + 42, 3 * 35 + 42, 3 * 11 + 6, 48 + 9, 34 + 9, 16 + 9, 20 + 9, 71 + 9, 66 + 9, 228 + 9]
-KNAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
-          "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final"]
 
 
 class ClockSampler:
@@ -95,16 +93,6 @@ class ClockSampler:
         return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def stripe_rows_for(height, n):
-    """Largest stripe height <= 8 such that every rank gets the same number of whole stripes."""
-    if n == 1:
-        return height
-    for s in (8, 6, 5, 4, 3, 2, 1):
-        if height % (s * n) == 0:
-            return s
-    return 1
-
-
 def run_gpu(args):
     import numpy as np
     import torch
@@ -133,16 +121,17 @@ def run_gpu(args):
     stream = torch.cuda.current_stream()
     r.set_stream(stream.cuda_stream)
 
-    srows = stripe_rows_for(H, world)
-    local_rows = H // world if world > 1 else H
-    frame_local = torch.empty((local_rows, W, 4), dtype=torch.uint8, device=dev)
+    from gpuraytracer_b200 import multigpu
+    srows = multigpu.stripe_rows_for(H, world)
+    pad_rows = multigpu.max_local_rows(H, srows, world) if world > 1 else H
+    frame_local = torch.empty((pad_rows, W, 4), dtype=torch.uint8, device=dev)
     gathered = [torch.empty_like(frame_local) for _ in range(world)] if (world > 1 and rank == 0) else None
     frame_full = torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else frame_local
     host_frame = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def frame(step, to_host):
-        """One step: update (host), dispatch, [gather], [D2H]."""
+        """One step: update (host), dispatch, [gather + compose on rank 0], [D2H]."""
         r.on_update(step / 60.0)
         if world == 1:
             if to_host:
@@ -151,12 +140,9 @@ def run_gpu(args):
                 r.do_raytracing(frame_local.data_ptr())
             return
         r.do_raytracing_striped(frame_local.data_ptr(), srows, rank, world)
-        dist.gather(frame_local, gathered, dst=0)
+        multigpu.gather_stripes(frame_local, gathered, dst=0)
         if rank == 0:
-            # un-interleave: rank k owns stripes k, k+world, ...
-            full = frame_full.view(H // (srows * world), world, srows, W, 4)
-            for k in range(world):
-                full[:, k].copy_(gathered[k].view(H // (srows * world), srows, W, 4))
+            multigpu.compose(frame_full, gathered, H, srows, world)
             if to_host:
                 host_frame.copy_(frame_full, non_blocking=True)
                 stream.synchronize()
@@ -240,44 +226,51 @@ def run_gpu(args):
 
 
 def roofline(args, conf, device, cfg, world):
-    """Per-kernel device times (CUDA events around every launch, on the launching stream) of full
-    single-GPU frames of the same workload; the dominant kernel's algorithmic FP32 work / time
-    against the measured FFMA peak, and the most memory-bound kernel's bytes / time against the
-    measured HBM copy bandwidth."""
+    """The dominant kernel of the step is the intersection kernel (all primitive types in one
+    persistent launch per wave).  Its launches are timed live with CUDA events on the launching
+    stream (GPRT_FLAG_PROFILE_KERNELS) over full single-GPU frames of the same workload, L2 flushed
+    between frames; achieved = algorithmic FP32 work of those launches (device work counters x the
+    hand-counted flops per unit of DESIGN.md section 5) / their duration, against the FP32-FMA
+    issue-rate peak measured in this run.  A second object does the same for the most
+    memory-bound kernel (the final fold) against the measured HBM copy bandwidth."""
+    import torch
     from gpuraytracer_b200 import Renderer
-    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS
+    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, KERNEL_NAMES
     cfg.flags = GPRT_FLAG_PROFILE_KERNELS
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", device))
     with Renderer(scene_id=conf["scene_id"], device=device, config=cfg) as r:
         r.on_init()
         W, H = r.width, r.height
-        ms = [0.0] * 14
+        nk = len(KERNEL_NAMES)
+        ms = [0.0] * nk
         work = [0] * 10
-        launches = [0] * 14
+        launches = [0] * nk
         reps = 5
         for i in range(2 + reps):
             r.on_update((args.warmup + i) / 60.0)
+            flush.zero_()
+            torch.cuda.synchronize()
             r.on_render()
             if i < 2:
                 continue
             p = r.kernel_profile()
-            for k in range(14):
+            for k in range(nk):
                 ms[k] += p.ms[k]
                 launches[k] += p.launches[k]
             for t in range(10):
                 work[t] += p.work[t]
         c = r.counters()
-        rays = int(c.radiance_rays) + int(c.shadow_rays)
+        depth = int(r.scene().config.max_recursion_depth)
         fp32_peak = r.measure_fp32_peak()
     cfg.flags = 0
     ms = [m / reps for m in ms]
     work = [w / reps for w in work]
     launches = [n // reps for n in launches]
-    kernel_ms = {KNAMES[k]: round(ms[k], 4) for k in range(14) if launches[k]}
-    # dominant kernel among the intersection kernels (type ids 0..9 -> kernel kinds 1..10)
-    dom = max(range(10), key=lambda t: ms[1 + t])
-    flops = work[dom] * FLOPS_PER_UNIT[dom]
-    dur = ms[1 + dom] * 1e-3
-    n_l = max(launches[1 + dom], 1)
+    kernel_ms = {KERNEL_NAMES[k]: round(ms[k], 4) for k in range(nk) if launches[k]}
+    dom = GPRT_K_INTERSECT_ALL
+    flops = sum(work[t] * FLOPS_PER_UNIT[t] for t in range(10))
+    dur = ms[dom] * 1e-3
+    n_l = max(launches[dom], 1)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -287,18 +280,21 @@ def roofline(args, conf, device, cfg, world):
     peak_src = "measured in this run: FFMA issue-rate probe (gprt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure"
     if not fp32_peak or fp32_peak <= 0:
         fp32_peak, peak_src = 74.4, "nominal fallback: 148 SMs x 128 lanes x 2 x 1.965 GHz"
-    roof = {"bound": "fp32", "kernel": KNAMES[1 + dom], "achieved": round(achieved, 3), "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
+    roof = {"bound": "fp32", "kernel": "k_intersect_coop (all primitive types, one persistent launch per wave)",
+            "achieved": round(achieved, 3), "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
             "frac": round(achieved / fp32_peak, 4), "traffic": None, "peak_source": peak_src,
-            "flops_per_launch": flops / n_l, "units_per_launch": work[dom] / n_l, "flops_per_unit": FLOPS_PER_UNIT[dom],
-            "launches_per_step": n_l, "avg_launch_ms": round(ms[1 + dom] / n_l, 4),
-            "note": "not a tensor-core path: the march kernels are FP32-issue bound (SURVEY.md 8d)"}
-    # memory-bound kernel: final fold = per pixel, per existing level 53 B of hit record read + 4 B written
-    levels = rays  # one hit record per radiance ray ~ radiance rays; bounded above by all rays
+            "flops_per_launch": round(flops / n_l), "launches_per_step": n_l, "avg_launch_ms": round(ms[dom] / n_l, 4),
+            "share_of_step": round(ms[dom] / max(sum(ms), 1e-9), 3),
+            "units_per_step": {KERNEL_NAMES[1 + t]: round(work[t]) for t in range(10) if work[t]},
+            "flops_per_unit": {KERNEL_NAMES[1 + t]: FLOPS_PER_UNIT[t] for t in range(10) if work[t]},
+            "note": "not a tensor-core path: the march kernels are FP32-issue bound (SURVEY.md 8d); the peak counts FMA as 2 flops while "
+                    "the IEEE parity build issues separate FMUL/FADD, so its ceiling is half of this peak"}
+    # memory-bound kernel: final fold = per pixel 4 B colour out + 4 B level code per level, plus 49 B of hit record per radiance hit
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    fin_bytes = W * H * (4 + 3 * 4) + int(c.radiance_rays) * 49
-    fin_dur = ms[13] * 1e-3
-    hbm = {"bound": "hbm", "kernel": "final", "achieved": round(fin_bytes / fin_dur / 1e9, 1) if fin_dur > 0 else 0.0, "peak": hbm_peak,
+    fin_bytes = W * H * (4 + depth * 4) + int(c.radiance_rays) * 49
+    fin_dur = ms[GPRT_K_FINAL] * 1e-3
+    hbm = {"bound": "hbm", "kernel": "k_final_color", "achieved": round(fin_bytes / fin_dur / 1e9, 1) if fin_dur > 0 else 0.0, "peak": hbm_peak,
            "unit": "GB/s", "frac": round(fin_bytes / fin_dur / 1e9 / hbm_peak, 4) if fin_dur > 0 else 0.0, "traffic": None,
            "peak_source": hbm_src, "bytes_per_launch": fin_bytes}
     return roof, hbm, kernel_ms

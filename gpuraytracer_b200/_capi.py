@@ -15,7 +15,7 @@ GPRT_ABI_VERSION = 1
 GPRT_MATH_PARITY, GPRT_MATH_FAST = 0, 1
 GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1
 GPRT_FLAG_PROFILE_KERNELS = 2
-GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14
+GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14, 15
 GPRT_HIT_MISS = 0xFFFFFFFF
 GPRT_HIT_TRIANGLE = 0x00000000
 GPRT_HIT_AABB = 0x10000000
@@ -42,7 +42,7 @@ class Counters(C.Structure):
 
 
 class KernelProfile(C.Structure):
-    _fields_ = [("ms", C.c_float * 14), ("launches", C.c_uint32 * 14), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
+    _fields_ = [("ms", C.c_float * 15), ("launches", C.c_uint32 * 15), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
 
 
 class WaveStats(C.Structure):
@@ -65,6 +65,10 @@ class SceneView(C.Structure):
 
 
 # numpy views of the ABI structs (sizes asserted against include/gprt.h in tests/test_abi.py)
+KERNEL_NAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
+                "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final", "intersect_all"]
+TYPE_NAMES = KERNEL_NAMES[1:11]
+
 SCENE_CB_DTYPE = np.dtype([("projection_to_world", "<f4", (4, 4)), ("camera_position", "<f4", 4), ("light_position", "<f4", 4),
                            ("light_ambient_color", "<f4", 4), ("light_diffuse_color", "<f4", 4), ("reflectance", "<f4"),
                            ("elapsed_time", "<f4"), ("_pad", "<f4", 2)])
@@ -100,6 +104,8 @@ def lib():
         "gprt_build_accel": (i32, [vp]),
         "gprt_refit_accel": (i32, [vp, vp, u32]),
         "gprt_dispatch": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp, vp]),
+        "gprt_dispatch_stripes": (i32, [vp, vp, vp, u32, u32, u32, u32, u32, u32, vp, C.c_size_t, vp]),
+        "gprt_stripe_local_rows": (u32, [u32, u32, u32, u32]),
         "gprt_dispatch_host": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp]),
         "gprt_sync": (i32, [vp]),
         "gprt_get_counters": (i32, [vp, C.POINTER(Counters)]),
@@ -118,6 +124,7 @@ def lib():
         "gprt_renderer_on_update": (i32, [vp, f32, f32, f32]),
         "gprt_renderer_on_render": (i32, [vp, Rect, vp, vp]),
         "gprt_renderer_do_raytracing": (i32, [vp, Rect, vp, vp, vp]),
+        "gprt_renderer_do_raytracing_stripes": (i32, [vp, u32, u32, u32, vp, vp]),
         "gprt_renderer_on_size_changed": (i32, [vp, u32, u32]),
         "gprt_renderer_scene": (i32, [vp, C.POINTER(SceneView)]),
         "gprt_renderer_context": (vp, [vp]),
@@ -134,10 +141,10 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "gprt_default_config", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
-    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_host", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
+    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
-    "gprt_renderer_do_raytracing", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
+    "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
 ]
 

@@ -284,7 +284,9 @@ struct ScopedInterval { // CUDA events around one launch when profiling is on
     ~ScopedInterval() { if (e1) cudaEventRecord(e1, c->stream); }
 };
 
-int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t height, gprt_rect pass, const OutputBuffers& ob, int band) {
+struct Stripes { uint32_t rows = 0, rank = 0, world = 1; };
+
+int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t height, gprt_rect pass, const OutputBuffers& ob, int band, const Stripes& st) {
     PassParams pp;
     std::memset(&pp, 0, sizeof pp);
     std::memcpy(pp.fc.projection_to_world, cb->projection_to_world, sizeof pp.fc.projection_to_world);
@@ -303,6 +305,7 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     pp.ray_capacity = 2 * pp.n_pixels;
     pp.cand_capacity = c->cand_capacity;
     pp.brute_force = (c->cfg.flags & GPRT_FLAG_BRUTE_FORCE_TRAVERSAL) ? 1u : 0u;
+    pp.stripe_rows = st.rows; pp.stripe_rank = st.rank; pp.stripe_world = st.world;
 
     const uint32_t D = pp.max_depth;
     GPRT_CUDA(c, cudaMemsetAsync(c->wb.ctrl, 0, sizeof(WaveCtrl) * (kMaxDepth + 2), c->stream));
@@ -310,13 +313,14 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     int launches = 0;
     for (uint32_t wave = 1; wave <= D; wave++) {
         { ScopedInterval si(c, GPRT_K_TRAVERSE); launches += c->kt->traverse(c->scene, pp, c->wb, (int)wave, c->stream); }
-        if ((c->cfg.flags & GPRT_FLAG_PROFILE_KERNELS) || c->per_type_launches) {
+        if (c->per_type_launches) {
             for (int t = 0; t < kNumTypes; t++)
                 if ((c->type_mask >> t) & 1u) {
                     ScopedInterval si(c, GPRT_K_INTERSECT0 + t);
                     launches += c->kt_isect->intersect(c->scene, pp, c->wb, (int)wave, t, (int)c->cfg.metaballs_count, c->stream);
                 }
         } else if (c->type_mask) {
+            ScopedInterval si(c, GPRT_K_INTERSECT_ALL);
             launches += c->kt_isect->intersect_all(c->scene, pp, c->wb, (int)wave, c->type_mask, (int)c->cfg.metaballs_count, c->stream);
         }
         if (c->type_mask) { ScopedInterval si(c, GPRT_K_RESOLVE); launches += c->kt->resolve(c->scene, pp, c->wb, (int)wave, c->type_mask, c->stream); }
@@ -482,11 +486,11 @@ int gprt_refit_accel(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs) {
     return GPRT_OK;
 }
 
-int gprt_dispatch(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
-                  uint32_t height, gprt_rect tile, void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids, float* d_rgba_f32) {
-    if (!c || !scene || !d_rgba8 || width == 0 || height == 0) return GPRT_E_INVALID_ARG;
-    if (!c->built) return GPRT_E_NOT_BUILT;
-    if (tile.w == 0 || tile.h == 0 || tile.x + tile.w > width || tile.y + tile.h > height) return GPRT_E_INVALID_ARG;
+namespace {
+// Common body of gprt_dispatch / gprt_dispatch_stripes.  `tile` is in global pixel coordinates, or
+// (striped) x/w in pixels and y/h in LOCAL rows of this rank.
+int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                  uint32_t height, gprt_rect tile, const Stripes& st, void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids, float* d_rgba_f32) {
     if (pitch_bytes < (size_t)tile.w * 4 || (pitch_bytes & 3u)) return GPRT_E_INVALID_ARG;
     if (n_per_frame && !per_frame) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaSetDevice(c->device));
@@ -537,13 +541,46 @@ int gprt_dispatch(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
         OutputBuffers ob;
         ob.rgba8 = (uint8_t*)d_rgba8; ob.pitch = pitch_bytes; ob.hit_ids = d_hit_ids; ob.rgba_f32 = (float4*)d_rgba_f32;
         ob.out_x0 = 0; ob.out_y0 = y0; ob.out_w = tile.w;
-        rc = run_pass(c, scene, width, height, pass, ob, band);
+        rc = run_pass(c, scene, width, height, pass, ob, band, st);
         if (rc != GPRT_OK) return rc;
     }
     c->n_bands_last = band;
     GPRT_CUDA(c, cudaEventRecord(c->ev_stop, c->stream));
     c->have_dispatch_timing = true;
     return GPRT_OK;
+}
+} // namespace
+
+int gprt_dispatch(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                  uint32_t height, gprt_rect tile, void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids, float* d_rgba_f32) {
+    if (!c || !scene || !d_rgba8 || width == 0 || height == 0) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    if (tile.w == 0 || tile.h == 0 || tile.x + tile.w > width || tile.y + tile.h > height) return GPRT_E_INVALID_ARG;
+    return dispatch_impl(c, scene, per_frame, n_per_frame, width, height, tile, Stripes(), d_rgba8, pitch_bytes, d_hit_ids, d_rgba_f32);
+}
+
+uint32_t gprt_stripe_local_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t world) {
+    if (stripe_rows == 0 || world == 0 || rank >= world) return 0;
+    const uint32_t period = stripe_rows * world;
+    const uint32_t full = height / period, rem = height % period;
+    uint32_t rows = full * stripe_rows;
+    const uint32_t lo = rank * stripe_rows;
+    if (rem > lo) rows += (rem - lo < stripe_rows) ? rem - lo : stripe_rows;
+    return rows;
+}
+
+int gprt_dispatch_stripes(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                          uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8, size_t pitch_bytes,
+                          uint32_t* d_hit_ids) {
+    if (!c || !scene || !d_rgba8 || width == 0 || height == 0) return GPRT_E_INVALID_ARG;
+    if (stripe_rows == 0 || world == 0 || rank >= world) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    const uint32_t rows = gprt_stripe_local_rows(height, stripe_rows, rank, world);
+    if (rows == 0) return GPRT_OK; // more ranks than stripes: nothing to render here
+    Stripes st;
+    st.rows = stripe_rows; st.rank = rank; st.world = world;
+    const gprt_rect tile = {0, 0, width, rows};
+    return dispatch_impl(c, scene, per_frame, n_per_frame, width, height, tile, st, d_rgba8, pitch_bytes, d_hit_ids, nullptr);
 }
 
 int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,

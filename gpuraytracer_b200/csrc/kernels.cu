@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(kBlock) k_traverse(const __grid_constant__ Sce
         V3 o, d;
         uint32_t meta;
         if (PRIMARY) {
-            const uint32_t px = pp.tile_x + r % pp.tile_w, py = pp.tile_y + r / pp.tile_w;
+            const uint32_t px = pp.tile_x + r % pp.tile_w, py = pass_global_row(pp, r / pp.tile_w);
             generate_camera_ray(px, py, pp.fc, o, d);
             meta = make_meta(r, 1u, 0u);
             wb.ray_o[pq][r] = make_float4(o.x, o.y, o.z, 0.0f);
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ 
                                                         const __grid_constant__ WaveBuffers wb, const __grid_constant__ OutputBuffers ob) {
     for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < pp.n_pixels; pixel += gridDim.x * blockDim.x) {
         const uint32_t tx = pixel % pp.tile_w, ty = pixel / pp.tile_w;
-        const uint32_t px = pp.tile_x + tx, py = pp.tile_y + ty;
+        const uint32_t px = pp.tile_x + tx, py = pass_global_row(pp, ty);
         V4 color = v4s(0.0f); // TraceRadianceRay beyond the depth limit returns 0 (src/Raytracing.hlsl:89-92)
         for (int level = (int)pp.max_depth; level >= 1; level--) {
             const size_t li = (size_t)(level - 1) * pp.n_pixels + pixel;

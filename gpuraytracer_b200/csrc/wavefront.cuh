@@ -81,7 +81,17 @@ struct PassParams {
     uint32_t ray_capacity;                   // 2 * n_pixels
     uint32_t cand_capacity;                  // per type
     uint32_t brute_force;
+    // multi-GPU row striping: with stripe_world > 1 the pass covers LOCAL rows tile_y .. tile_y+tile_h of
+    // rank stripe_rank, local row l being global row ((l / stripe_rows) * stripe_world + stripe_rank) *
+    // stripe_rows + l % stripe_rows.  DispatchRaysIndex / Dimensions stay global either way.
+    uint32_t stripe_rows, stripe_rank, stripe_world;
 };
+
+__host__ __device__ inline uint32_t pass_global_row(const PassParams& pp, uint32_t ty) {
+    const uint32_t l = pp.tile_y + ty;
+    if (pp.stripe_world <= 1u) return l;
+    return ((l / pp.stripe_rows) * pp.stripe_world + pp.stripe_rank) * pp.stripe_rows + l % pp.stripe_rows;
+}
 
 struct WaveBuffers {
     float4* ray_o[2];  // ping-pong by wave parity: xyz origin

@@ -96,6 +96,13 @@ int Renderer::do_raytracing(gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, 
                          m_scene.height, tile, d_rgba8, (size_t)tile.w * 4, d_hit_ids, d_rgba_f32);
 }
 
+int Renderer::do_raytracing_stripes(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8, uint32_t* d_hit_ids) {
+    if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
+    m_last_tile = {0, 0, m_scene.width, gprt_stripe_local_rows(m_scene.height, stripe_rows, rank, world)};
+    return gprt_dispatch_stripes(m_ctx, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
+                                 m_scene.height, stripe_rows, rank, world, d_rgba8, (size_t)m_scene.width * 4, d_hit_ids);
+}
+
 int Renderer::on_render(gprt_rect tile, void* h_rgba8, uint32_t* h_hit_ids) {
     if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
     tile = full_if_empty(tile, m_scene);
@@ -144,6 +151,10 @@ int gprt_renderer_on_render(gprt_renderer* r, gprt_rect tile, void* h_rgba8, uin
 }
 int gprt_renderer_do_raytracing(gprt_renderer* r, gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, float* d_rgba_f32) {
     return r ? r->impl.do_raytracing(tile, d_rgba8, d_hit_ids, d_rgba_f32) : GPRT_E_INVALID_ARG;
+}
+int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8,
+                                        uint32_t* d_hit_ids) {
+    return r ? r->impl.do_raytracing_stripes(stripe_rows, rank, world, d_rgba8, d_hit_ids) : GPRT_E_INVALID_ARG;
 }
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t w, uint32_t h) {
     return r ? r->impl.on_size_changed(w, h) : GPRT_E_INVALID_ARG;

@@ -21,6 +21,8 @@ public:
     void on_destroy();                                           // :163-170
 
     int do_raytracing(gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, float* d_rgba_f32); // :401-452
+    // multi-GPU: this rank's row stripes only (gprt_dispatch_stripes), packed output
+    int do_raytracing_stripes(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8, uint32_t* d_hit_ids);
     float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399
 
     SceneState& scene() { return m_scene; }

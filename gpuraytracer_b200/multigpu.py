@@ -1,0 +1,74 @@
+"""Tile sharding of one frame across the GPUs of a box.
+
+The path shards by pixels: the scene is replicated (every rank builds the same LBVH from the same
+inputs), rank r renders the row stripes r, r + world, ... (gprt_dispatch_stripes) and the RGBA8 rows
+are gathered to rank 0 -- the only exchange step of the path.  Stripes are a few rows high and
+interleaved so that the expensive regions of the image (the fractal pyramid, the metaballs) are
+spread over all ranks.
+
+torch.distributed is plumbing here: NCCL over NVLink on the GPU box (gather = grouped send/recv),
+gloo in the CPU tests.  Nothing is computed in this module.
+"""
+import numpy as np
+
+from ._capi import lib
+
+
+def stripe_rows_for(height: int, world: int, max_rows: int = 8) -> int:
+    """Largest stripe height <= max_rows that gives every rank the same number of whole stripes
+    (so that the gather needs no padding); 1 if there is none."""
+    if world <= 1:
+        return max(int(height), 1)
+    for s in range(max_rows, 0, -1):
+        if height % (s * world) == 0:
+            return s
+    return 1
+
+
+def local_rows(height: int, stripe_rows: int, rank: int, world: int) -> int:
+    """Rows rank `rank` renders (C ABI: gprt_stripe_local_rows)."""
+    return int(lib().gprt_stripe_local_rows(int(height), int(stripe_rows), int(rank), int(world)))
+
+
+def global_rows(height: int, stripe_rows: int, rank: int, world: int) -> np.ndarray:
+    """Global row index of every local row of `rank`, in local order."""
+    n = local_rows(height, stripe_rows, rank, world)
+    l = np.arange(n, dtype=np.int64)
+    return ((l // stripe_rows) * world + rank) * stripe_rows + l % stripe_rows
+
+
+def max_local_rows(height: int, stripe_rows: int, world: int) -> int:
+    return max(local_rows(height, stripe_rows, r, world) for r in range(world))
+
+
+def gather_stripes(local, gathered, dst=0, group=None):
+    """Gather every rank's packed stripe buffer (same shape on all ranks, padded to max_local_rows)
+    to rank `dst`.  `gathered` is a list of world tensors on dst, None elsewhere."""
+    import torch.distributed as dist
+    dist.gather(local, gathered if dist.get_rank(group) == dst else None, dst=dst, group=group)
+
+
+def compose(full, gathered, height: int, stripe_rows: int, world: int):
+    """Un-interleave the gathered stripe buffers into the full frame `full` [H, W, 4] (torch tensors
+    or numpy arrays; index copies only)."""
+    if height % (stripe_rows * world) == 0:
+        # regular case: one strided copy per rank
+        groups = height // (stripe_rows * world)
+        view = full.reshape(groups, world, stripe_rows, *full.shape[1:])
+        for r in range(world):
+            src = gathered[r][:groups * stripe_rows].reshape(groups, stripe_rows, *full.shape[1:])
+            if hasattr(view, "copy_"):
+                view[:, r].copy_(src)
+            else:
+                view[:, r] = src
+        return full
+    for r in range(world):
+        rows = global_rows(height, stripe_rows, r, world)
+        if len(rows) == 0:
+            continue
+        if hasattr(full, "index_copy_"):
+            import torch
+            full.index_copy_(0, torch.as_tensor(rows, device=full.device), gathered[r][:len(rows)])
+        else:
+            full[rows] = gathered[r][:len(rows)]
+    return full

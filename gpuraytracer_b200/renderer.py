@@ -79,6 +79,11 @@ class Renderer:
         rect, _, _ = self._tile(tile)
         check(self._lib.gprt_renderer_do_raytracing(self._h, rect, d_rgba8_ptr, d_hit_ids_ptr, d_rgba_f32_ptr), "do_raytracing")
 
+    def do_raytracing_striped(self, d_rgba8_ptr, stripe_rows, rank, world, d_hit_ids_ptr=None):
+        """Multi-GPU: render this rank's row stripes into a packed DEVICE buffer (asynchronous)."""
+        check(self._lib.gprt_renderer_do_raytracing_stripes(self._h, int(stripe_rows), int(rank), int(world), d_rgba8_ptr, d_hit_ids_ptr),
+              "do_raytracing_stripes")
+
     def sync(self):
         check(self._lib.gprt_sync(self.context), "sync")
 

@@ -148,8 +148,10 @@ typedef struct gprt_counters {
 
 /* Per-kernel device time of the last dispatch (only with GPRT_FLAG_PROFILE_KERNELS) and the work
  * each intersection kernel did (always counted). */
-enum { GPRT_K_TRAVERSE = 0, GPRT_K_INTERSECT0 = 1 /* + type id 0..9 */, GPRT_K_RESOLVE = 11, GPRT_K_SHADE_SPAWN = 12,
-       GPRT_K_FINAL = 13, GPRT_K_COUNT = 14 };
+enum { GPRT_K_TRAVERSE = 0, GPRT_K_INTERSECT0 = 1 /* + type id 0..9: one launch per type, only with GPRT_PER_TYPE_LAUNCHES=1 */,
+       GPRT_K_RESOLVE = 11, GPRT_K_SHADE_SPAWN = 12, GPRT_K_FINAL = 13,
+       GPRT_K_INTERSECT_ALL = 14 /* the production intersection kernel: all types in one persistent launch per wave */,
+       GPRT_K_COUNT = 15 };
 typedef struct gprt_kernel_profile {
     float    ms[GPRT_K_COUNT];
     uint32_t launches[GPRT_K_COUNT];
@@ -242,6 +244,19 @@ int gprt_dispatch_host(gprt_ctx* ctx, const gprt_scene_cb* scene,
                        const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
                        uint32_t width, uint32_t height, gprt_rect tile,
                        void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids);
+
+/* Multi-GPU sharding (no counterpart in the single-GPU reference): the frame is cut into stripes of
+ * `stripe_rows` rows dealt round-robin to `world` ranks; rank r renders stripes r, r + world, ...
+ * into a PACKED buffer of gprt_stripe_local_rows() rows (local row l at d_rgba8 + l * pitch_bytes,
+ * local row l = global row ((l / stripe_rows) * world + r) * stripe_rows + l % stripe_rows).
+ * DispatchRaysIndex / DispatchRaysDimensions stay global, so the union of all ranks' rows is
+ * bit-identical to one full-frame gprt_dispatch.  Asynchronous on the context stream. */
+int gprt_dispatch_stripes(gprt_ctx* ctx, const gprt_scene_cb* scene,
+                          const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
+                          uint32_t width, uint32_t height,
+                          uint32_t stripe_rows, uint32_t rank, uint32_t world,
+                          void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids);
+uint32_t gprt_stripe_local_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t world);
 
 #define GPRT_HIT_MISS     0xFFFFFFFFu
 #define GPRT_HIT_TRIANGLE 0x00000000u /* | PrimitiveIndex()  (instance 0)               */

@@ -56,6 +56,10 @@ int gprt_renderer_on_render(gprt_renderer* r, gprt_rect tile, void* h_rgba8, uin
 /* do_raytracing only, output left in device memory (tile-packed); asynchronous. */
 int gprt_renderer_do_raytracing(gprt_renderer* r, gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids,
                                 float* d_rgba_f32);
+/* Multi-GPU: do_raytracing over this rank's row stripes only (gprt_dispatch_stripes); the output is
+ * gprt_stripe_local_rows() packed rows of width * 4 bytes in device memory; asynchronous. */
+int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world,
+                                        void* d_rgba8, uint32_t* d_hit_ids);
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);
 
 int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out);

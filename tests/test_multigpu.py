@@ -1,0 +1,114 @@
+"""Multi-GPU sharding: host logic on CPU (gloo, world_size 2 and 3) and the striped dispatch on the GPU."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+from gpuraytracer_b200 import multigpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.mark.parametrize("height,srows,world", [(1080, 5, 8), (1080, 8, 8), (17, 3, 2), (5, 2, 4), (4320, 6, 8), (480, 8, 1), (7, 16, 3)])
+def test_stripes_partition_the_frame(height, srows, world):
+    rows = [multigpu.global_rows(height, srows, r, world) for r in range(world)]
+    assert [len(x) for x in rows] == [multigpu.local_rows(height, srows, r, world) for r in range(world)]
+    allr = np.sort(np.concatenate(rows))
+    np.testing.assert_array_equal(allr, np.arange(height))  # every row exactly once
+    for r, x in enumerate(rows):
+        assert ((x // srows) % world == r).all()
+
+
+def test_stripe_rows_for_gives_equal_shares():
+    for h, w in [(1080, 2), (1080, 4), (1080, 8), (4320, 8), (2160, 8), (480, 3), (17, 2)]:
+        s = multigpu.stripe_rows_for(h, w)
+        assert 1 <= s <= 8
+        if h % w == 0:
+            assert len({multigpu.local_rows(h, s, r, w) for r in range(w)}) == 1
+    assert multigpu.stripe_rows_for(1080, 1) == 1080
+
+
+def test_compose_irregular_numpy():
+    h, w, srows, world = 23, 5, 3, 4
+    full = np.random.default_rng(0).integers(0, 255, (h, w, 4), dtype=np.uint8)
+    pad = multigpu.max_local_rows(h, srows, world)
+    gathered = []
+    for r in range(world):
+        buf = np.zeros((pad, w, 4), np.uint8)
+        rows = multigpu.global_rows(h, srows, r, world)
+        buf[:len(rows)] = full[rows]
+        gathered.append(buf)
+    out = multigpu.compose(np.zeros_like(full), gathered, h, srows, world)
+    np.testing.assert_array_equal(out, full)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, height_crop, srows, out_path):
+    """One rank of the sharded frame on CPU: its stripes come from a committed golden image (the
+    oracle's output for config 1), the exchange + composition are the package's own."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from gpuraytracer_b200 import multigpu as mg
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    golden = np.load(os.path.join(GOLDEN, "config1.npz"))["rgba8"][:height_crop]
+    h, w = golden.shape[:2]
+    pad = mg.max_local_rows(h, srows, world)
+    local = torch.zeros((pad, w, 4), dtype=torch.uint8)
+    rows = mg.global_rows(h, srows, rank, world)
+    local[:len(rows)] = torch.from_numpy(golden[rows])  # stands in for gprt_dispatch_stripes
+    gathered = [torch.zeros_like(local) for _ in range(world)] if rank == 0 else None
+    mg.gather_stripes(local, gathered, dst=0)
+    if rank == 0:
+        full = mg.compose(torch.zeros((h, w, 4), dtype=torch.uint8), gathered, h, srows, world)
+        np.save(out_path, full.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,height_crop,srows", [(2, 480, 8), (2, 477, 5), (3, 100, 4)])
+def test_gather_and_compose_over_gloo(tmp_path, world, height_crop, srows):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "full.npy")
+    mp.spawn(_worker, args=(world, _free_port(), height_crop, srows, out), nprocs=world, join=True)
+    golden = np.load(os.path.join(GOLDEN, "config1.npz"))["rgba8"][:height_crop]
+    np.testing.assert_array_equal(np.load(out), golden)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,srows,height", [(2, 8, 180), (4, 5, 180), (8, 3, 181), (3, 7, 90)])
+def test_striped_dispatch_equals_full_frame(world, srows, height):
+    """All ranks' stripes (each rendered by gprt_dispatch_stripes on this one GPU) compose to a frame
+    bit-identical to the full dispatch, hit ids included."""
+    import torch
+    from gpuraytracer_b200 import Renderer, default_config
+    cfg = default_config()
+    cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0
+    with Renderer(scene_id=0, width=320, height=height, device=0, config=cfg) as r:
+        r.on_init()
+        r.on_update(0.3)
+        full, full_ids = r.on_render(want_hit_ids=True)
+        r.set_stream(torch.cuda.current_stream().cuda_stream)
+        pad = multigpu.max_local_rows(height, srows, world)
+        gathered, gathered_ids = [], []
+        for rank in range(world):
+            buf = torch.zeros((pad, 320, 4), dtype=torch.uint8, device="cuda")
+            ids = torch.zeros((pad, 320), dtype=torch.int32, device="cuda")
+            r.do_raytracing_striped(buf.data_ptr(), srows, rank, world, d_hit_ids_ptr=ids.data_ptr())
+            r.sync()
+            gathered.append(buf)
+            gathered_ids.append(ids)
+        out = multigpu.compose(torch.zeros((height, 320, 4), dtype=torch.uint8, device="cuda"), gathered, height, srows, world)
+        out_ids = multigpu.compose(torch.zeros((height, 320), dtype=torch.int32, device="cuda"), gathered_ids, height, srows, world)
+    np.testing.assert_array_equal(out.cpu().numpy(), full)
+    np.testing.assert_array_equal(out_ids.cpu().numpy().view(np.uint32), full_ids)

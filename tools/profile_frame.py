@@ -17,8 +17,7 @@ import numpy as np  # noqa: E402
 from gpuraytracer_b200 import Renderer, default_config  # noqa: E402
 from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS  # noqa: E402
 
-KNAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
-          "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final"]
+from gpuraytracer_b200._capi import KERNEL_NAMES as KNAMES  # noqa: E402
 
 
 def main():
@@ -32,7 +31,10 @@ def main():
     ap.add_argument("--time", type=float, default=0.0)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--save", default="")
+    ap.add_argument("--per-type", action="store_true", help="one intersection launch per primitive type (GPRT_PER_TYPE_LAUNCHES=1)")
     a = ap.parse_args()
+    if a.per_type:
+        os.environ["GPRT_PER_TYPE_LAUNCHES"] = "1"
 
     cfg = default_config()
     cfg.math_mode = 1 if a.fast else 0
@@ -54,7 +56,7 @@ def main():
             out["build_ms"] = r.timing().build_accel_ms
             if flags:
                 p = r.kernel_profile()
-                out["kernel_ms"] = {KNAMES[i]: round(p.ms[i], 4) for i in range(14) if p.launches[i]}
+                out["kernel_ms"] = {KNAMES[i]: round(p.ms[i], 4) for i in range(15) if p.launches[i]}
                 out["work"] = {KNAMES[1 + t]: int(p.work[t]) for t in range(10) if p.candidates[t]}
                 out["candidates"] = {KNAMES[1 + t]: int(p.candidates[t]) for t in range(10) if p.candidates[t]}
                 out["fp32_peak_tflops"] = round(r.measure_fp32_peak(), 2)

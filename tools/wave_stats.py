@@ -11,6 +11,7 @@ import os
 import sys
 
 os.environ.setdefault("GPRT_ISECT_VARIANT", "-1")
+os.environ.setdefault("GPRT_PER_TYPE_LAUNCHES", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 from gpuraytracer_b200 import Renderer, default_config  # noqa: E402
