@@ -49,12 +49,13 @@ __device__ __forceinline__ float sdf_distance_dyn(int sdf, V3 p) {
 }
 
 // fetch_candidate / publish for a run-time SDF type (the queues are indexed by type id = sdf + 3)
-__device__ __forceinline__ bool fetch_candidate_dyn(const SceneDev& sc, const WaveBuffers& wb, int pq, int type, uint32_t c, CandState& s) {
+__device__ __forceinline__ bool fetch_candidate_dyn(const SceneDev& sc, const WaveBuffers& wb, int pq, int type, uint32_t c, CandState& s, bool& shadow) {
     const uint2 cand = wb.cand[type][c];
     s.c = c; s.r = cand.x; s.prim = cand.y;
     const float4 rd = wb.ray_d[pq][s.r];
     const uint32_t meta = __float_as_uint(rd.w);
-    if (meta_shadow(meta) && wb.hitkey[s.r] != kKeyMiss) {
+    shadow = meta_shadow(meta) != 0u;
+    if (shadow && wb.hitkey[s.r] != kKeyMiss) {
         wb.cand_res[type][c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
         return false;
     }
@@ -103,13 +104,25 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
     bool active = false;
     int mode = 0; // 0: needs the field at p(t); 1: hit candidate at pos, needs the 4 taps (+ next sample)
     uint32_t step = 0, work = 0;
-    float t = 0.0f, dist_hit = 0.0f;
+    float t = 0.0f, dist_hit = 0.0f, t_stop = 0.0f;
+    bool shadow = false;
     V3 pos = v3s(0.0f);
 
     for (;;) {
+        // Early out against what other candidates of the same ray have committed meanwhile (the hit key
+        // lives in L2, hence __ldcg).  A shadow ray needs any hit (ACCEPT_FIRST_HIT_AND_END_SEARCH); a
+        // radiance ray keeps the closest, so samples beyond the committed t cannot win the atomicMin --
+        // the same shrinking RayTCurrent() a DXR traversal would show this shader.  The image is unchanged.
+        if (active) {
+            const unsigned long long key = __ldcg(&wb.hitkey[s.r]);
+            if (key != kKeyMiss) {
+                if (shadow) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
+                else t_stop = fminf(t_stop, __uint_as_float((uint32_t)(key >> 32)));
+            }
+        }
         const uint32_t idx = warp_take(q, refill_now<RMIN>(active) && !active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand && fetch_candidate_dyn(sc, wb, pq, TYPE, idx, s)) {
-            active = true; mode = 0; step = 0; t = s.lr.tmin;
+        if (idx != kNoCand && fetch_candidate_dyn(sc, wb, pq, TYPE, idx, s, shadow)) {
+            active = true; mode = 0; step = 0; t = s.lr.tmin; t_stop = s.lr.tcur;
         }
         if (!__any_sync(kFull, active)) {
             if (q.exhausted && q.next >= q.end) break;
@@ -118,7 +131,7 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
 #pragma unroll 1
         for (int trip = 0; trip < kTrips; trip++) {
             // while (i++ < MaxSteps && t <= RayTCurrent())
-            if (active && mode == 0 && !(step < max_steps && t <= s.lr.tcur)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
+            if (active && mode == 0 && !(step < max_steps && t <= t_stop)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
             const unsigned b1 = __ballot_sync(kFull, active && mode == 0), b5 = __ballot_sync(kFull, active && mode == 1);
             if (!(b1 | b5)) break;
             const uint32_t my_off = (uint32_t)__popc(b1 & lt) + 5u * (uint32_t)__popc(b5 & lt);
@@ -159,7 +172,7 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
                     } else {
                         t = t_next;
                         mode = 0;
-                        if (!(step < max_steps && t <= s.lr.tcur)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
+                        if (!(step < max_steps && t <= t_stop)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
                         else { dist = sdist[my_off + 4]; have_sample = true; }
                     }
                 }
