@@ -106,6 +106,8 @@ def lib():
         "gprt_dispatch": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp, vp]),
         "gprt_dispatch_stripes": (i32, [vp, vp, vp, u32, u32, u32, u32, u32, u32, vp, C.c_size_t, vp]),
         "gprt_stripe_local_rows": (u32, [u32, u32, u32, u32]),
+        "gprt_dispatch_host_async": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp]),
+        "gprt_get_stream": (vp, [vp]),
         "gprt_dispatch_host": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp]),
         "gprt_sync": (i32, [vp]),
         "gprt_get_counters": (i32, [vp, C.POINTER(Counters)]),
@@ -125,6 +127,10 @@ def lib():
         "gprt_renderer_on_render": (i32, [vp, Rect, vp, vp]),
         "gprt_renderer_do_raytracing": (i32, [vp, Rect, vp, vp, vp]),
         "gprt_renderer_do_raytracing_stripes": (i32, [vp, u32, u32, u32, vp, vp]),
+        "gprt_renderer_on_render_async": (i32, [vp, vp]),
+        "gprt_renderer_do_raytracing_async": (i32, [vp, vp]),
+        "gprt_renderer_wait_for_gpu": (i32, [vp]),
+        "gprt_renderer_frame_context": (vp, [vp, i32]),
         "gprt_renderer_on_size_changed": (i32, [vp, u32, u32]),
         "gprt_renderer_scene": (i32, [vp, C.POINTER(SceneView)]),
         "gprt_renderer_context": (vp, [vp]),
@@ -141,10 +147,11 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "gprt_default_config", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
-    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
+    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_dispatch_host_async", "gprt_get_stream", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
-    "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
+    "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_render_async", "gprt_renderer_do_raytracing_async",
+    "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
 ]
 

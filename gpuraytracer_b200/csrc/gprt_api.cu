@@ -356,7 +356,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     if (c0.max_recursion_depth < 1 || c0.max_recursion_depth > (uint32_t)kMaxDepth) return GPRT_E_UNSUPPORTED;
     if (c0.metaballs_count != 3 && c0.metaballs_count != 5) return GPRT_E_UNSUPPORTED;
     if (c0.metaball_max_steps == 0 || c0.sdf_max_steps == 0) return GPRT_E_INVALID_ARG;
-    if (c0.metaball_max_steps > 0xFFFFu) return GPRT_E_UNSUPPORTED; // the pool marcher packs the step count in 16 bits
+    if (c0.metaball_max_steps > 0xFFFFu || c0.sdf_max_steps > 0xFFFFu) return GPRT_E_UNSUPPORTED; // march states pack the step count in 16 bits
     if (c0.math_mode != GPRT_MATH_PARITY && c0.math_mode != GPRT_MATH_FAST) return GPRT_E_INVALID_ARG;
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
@@ -583,8 +583,8 @@ int gprt_dispatch_stripes(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_pr
     return dispatch_impl(c, scene, per_frame, n_per_frame, width, height, tile, st, d_rgba8, pitch_bytes, d_hit_ids, nullptr);
 }
 
-int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
-                       uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
+int gprt_dispatch_host_async(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                             uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
     if (!c || !h_rgba8) return GPRT_E_INVALID_ARG;
     if (tile.w == 0 || tile.h == 0) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaSetDevice(c->device));
@@ -600,8 +600,16 @@ int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_
     if (rc != GPRT_OK) return rc;
     GPRT_CUDA(c, cudaMemcpy2DAsync(h_rgba8, pitch_bytes, c->d_fb, (size_t)tile.w * 4, (size_t)tile.w * 4, tile.h, cudaMemcpyDeviceToHost, c->stream));
     if (h_hit_ids) GPRT_CUDA(c, cudaMemcpyAsync(h_hit_ids, c->d_fb_ids, pixels * 4, cudaMemcpyDeviceToHost, c->stream));
-    return gprt_sync(c);
+    return GPRT_OK;
 }
+
+int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
+                       uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
+    const int rc = gprt_dispatch_host_async(c, scene, per_frame, n_per_frame, width, height, tile, h_rgba8, pitch_bytes, h_hit_ids);
+    return rc != GPRT_OK ? rc : gprt_sync(c);
+}
+
+void* gprt_get_stream(gprt_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 int gprt_sync(gprt_ctx* c) {
     if (!c) return GPRT_E_INVALID_ARG;

@@ -457,8 +457,7 @@ template <int NB> void launch_all_v(const SceneDev& sc, const PassParams& pp, co
     switch (isect_variant()) {
     case -1: launch_all_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
     case 16: launch_all_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
-    case 201: launch_coop_t<NB, 1>(sc, pp, wb, wave, type_mask, s); break;
-    case 216: launch_coop_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
+    case 200: launch_coop_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
     default: launch_coop_t<NB, 8>(sc, pp, wb, wave, type_mask, s); break;
     }
 }

@@ -48,46 +48,77 @@ __device__ __forceinline__ float sdf_distance_dyn(int sdf, V3 p) {
     }
 }
 
-// fetch_candidate / publish for a run-time SDF type (the queues are indexed by type id = sdf + 3)
-__device__ __forceinline__ bool fetch_candidate_dyn(const SceneDev& sc, const WaveBuffers& wb, int pq, int type, uint32_t c, CandState& s, bool& shadow) {
+// One lane's march state.  The candidate's identity (ray slot, primitive, transforms) is re-read
+// from the queue entry `c` when the lane publishes a hit, so the state stays small enough to be
+// moved between lanes (pool compaction below).
+struct MarchLane {
+    V3 o, d;        // ray in the primitive's local space
+    float tcur;     // RayTCurrent() of the intersection shader (range test of ReportHit / IsAValidHit)
+    float t_stop;   // loop bound: min(tcur, closest t another candidate of the ray has committed)
+    float t, scale, dist_hit;
+    uint32_t c, r;  // queue entry, ray slot
+    uint32_t step;
+    int mode;       // 0: needs the field at p(t); 1: hit candidate at p(t), needs the 4 taps (+ next sample)
+    bool active, shadow;
+};
+
+// GetRayInAABBPrimitiveLocalSpace (src/Raytracing.hlsl:277-287) for queue entry c of type id `type`.
+// Returns false (after writing a "no hit" result) for a shadow ray that is already occluded.
+__device__ __forceinline__ bool fetch_lane(const SceneDev& sc, const WaveBuffers& wb, int pq, int type, uint32_t c, MarchLane& m) {
     const uint2 cand = wb.cand[type][c];
-    s.c = c; s.r = cand.x; s.prim = cand.y;
-    const float4 rd = wb.ray_d[pq][s.r];
-    const uint32_t meta = __float_as_uint(rd.w);
-    shadow = meta_shadow(meta) != 0u;
-    if (shadow && wb.hitkey[s.r] != kKeyMiss) {
+    m.c = c; m.r = cand.x;
+    const float4 rd = wb.ray_d[pq][m.r];
+    m.shadow = meta_shadow(__float_as_uint(rd.w)) != 0u;
+    if (m.shadow && wb.hitkey[m.r] != kKeyMiss) {
         wb.cand_res[type][c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
         return false;
     }
-    const float4 ro = wb.ray_o[pq][s.r];
-    const PrimRecord* pr = sc.prims + s.prim;
-    s.step_scale = pr->mat.step_scale;
-    s.pf = sc.per_frame + 32 * (size_t)pr->instance_index;
+    const float4 ro = wb.ray_o[pq][m.r];
+    const PrimRecord* pr = sc.prims + cand.y;
+    m.scale = pr->mat.step_scale;
+    const float* pf = sc.per_frame + 32 * (size_t)pr->instance_index;
     const V3 oo = xform_point_3x4(sc.aabb_w2o, ld3(ro)), dd = xform_vector_3x4(sc.aabb_w2o, ld3(rd));
-    s.lr.o = mul_point_rowvec(oo, s.pf + 16);
-    s.lr.d = mul_vector_rowvec(dd, s.pf + 16);
-    s.lr.tmin = 0.0f;
-    s.lr.tcur = wb.ray_tcur[s.r];
+    m.o = mul_point_rowvec(oo, pf + 16);
+    m.d = mul_vector_rowvec(dd, pf + 16);
+    m.tcur = wb.ray_tcur[m.r];
+    m.t_stop = m.tcur;
+    m.t = 0.0f; // RayTMin()
+    m.step = 0; m.mode = 0; m.dist_hit = 0.0f;
+    m.active = true;
     return true;
 }
-__device__ __forceinline__ void publish_hit_dyn(const SceneDev& sc, const WaveBuffers& wb, int type, const CandState& s, float thit, V3 n_local) {
-    if (thit >= s.lr.tmin && thit <= s.lr.tcur) {
-        const V3 nb = mul_vector_rowvec(n_local, s.pf);
+
+// ReportHit + the normal transform of the intersection shaders (src/Raytracing.hlsl:297-304)
+__device__ __forceinline__ void publish_lane_hit(const SceneDev& sc, const WaveBuffers& wb, int type, const MarchLane& m, float thit, V3 n_local) {
+    if (thit >= 0.0f && thit <= m.tcur) {
+        const uint32_t prim = wb.cand[type][m.c].y;
+        const float* pf = sc.per_frame + 32 * (size_t)sc.prims[prim].instance_index;
+        const V3 nb = mul_vector_rowvec(n_local, pf);
         const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
-        atomicMin(&wb.hitkey[s.r], pack_key(thit, s.prim));
-        wb.cand_res[type][s.c] = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
+        atomicMin(&wb.hitkey[m.r], pack_key(thit, prim));
+        wb.cand_res[type][m.c] = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
     } else {
-        wb.cand_res[type][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        wb.cand_res[type][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
     }
 }
 
-template <int RMIN>
-__device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq,
+// Early out against what other candidates of the same ray have committed meanwhile (the hit key
+// lives in L2, hence __ldcg).  A shadow ray needs any hit (ACCEPT_FIRST_HIT_AND_END_SEARCH); a
+// radiance ray keeps the closest, so samples beyond the committed t cannot win the atomicMin --
+// the same shrinking RayTCurrent() a DXR traversal would show this shader.  The image is unchanged.
+__device__ __forceinline__ void poll_committed(const WaveBuffers& wb, int type, MarchLane& m) {
+    if (!m.active) return;
+    const unsigned long long key = __ldcg(&wb.hitkey[m.r]);
+    if (key == kKeyMiss) return;
+    if (m.shadow) { wb.cand_res[type][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); m.active = false; }
+    else m.t_stop = fminf(m.t_stop, __uint_as_float((uint32_t)(key >> 32)));
+}
+
+// Up to `trips` cooperative trips of the warp (see the header comment).  Returns the number of
+// field evaluations the reference's loop would have made for this lane's candidate.
+__device__ __forceinline__ uint32_t coop_trips(const int SDF, MarchLane& m, int trips, const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb,
                                                int lane, CoopSmem& sm) {
     const int TYPE = SDF + 3;
-    constexpr int kTrips = 8; // loop trips between refill checks
-    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
-    if (count == 0) return;
     const int warp = threadIdx.x >> 5;
     float* const spx = sm.px[warp];
     float* const spy = sm.py[warp];
@@ -98,125 +129,356 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
     // tetrahedral taps of sdCalculateNormal: e.xyy, e.yyx, e.yxy, e.xxx
     const float ex = 1.0f * 0.5773f * 0.0001f, ey = -1.0f * 0.5773f * 0.0001f;
     const unsigned lt = (1u << lane) - 1u;
-
-    WarpChunk q;
-    CandState s;
-    bool active = false;
-    int mode = 0; // 0: needs the field at p(t); 1: hit candidate at pos, needs the 4 taps (+ next sample)
-    uint32_t step = 0, work = 0;
-    float t = 0.0f, dist_hit = 0.0f, t_stop = 0.0f;
-    bool shadow = false;
-    V3 pos = v3s(0.0f);
-
-    for (;;) {
-        // Early out against what other candidates of the same ray have committed meanwhile (the hit key
-        // lives in L2, hence __ldcg).  A shadow ray needs any hit (ACCEPT_FIRST_HIT_AND_END_SEARCH); a
-        // radiance ray keeps the closest, so samples beyond the committed t cannot win the atomicMin --
-        // the same shrinking RayTCurrent() a DXR traversal would show this shader.  The image is unchanged.
-        if (active) {
-            const unsigned long long key = __ldcg(&wb.hitkey[s.r]);
-            if (key != kKeyMiss) {
-                if (shadow) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
-                else t_stop = fminf(t_stop, __uint_as_float((uint32_t)(key >> 32)));
+    uint32_t evals = 0;
+#pragma unroll 1
+    for (int trip = 0; trip < trips; trip++) {
+        // while (i++ < MaxSteps && t <= RayTCurrent())
+        if (m.active && m.mode == 0 && !(m.step < max_steps && m.t <= m.t_stop)) {
+            wb.cand_res[TYPE][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+            m.active = false;
+        }
+        const unsigned b1 = __ballot_sync(kFull, m.active && m.mode == 0), b5 = __ballot_sync(kFull, m.active && m.mode == 1);
+        if (!(b1 | b5)) break;
+        const uint32_t my_off = (uint32_t)__popc(b1 & lt) + 5u * (uint32_t)__popc(b5 & lt);
+        const uint32_t total = (uint32_t)__popc(b1) + 5u * (uint32_t)__popc(b5);
+        float t_next = 0.0f;
+        V3 pos = v3s(0.0f);
+        if (m.active) {
+            pos = m.o + m.t * m.d;
+            if (m.mode == 0) {
+                spx[my_off] = pos.x; spy[my_off] = pos.y; spz[my_off] = pos.z;
+            } else {
+                spx[my_off + 0] = pos.x + ex; spy[my_off + 0] = pos.y + ey; spz[my_off + 0] = pos.z + ey;
+                spx[my_off + 1] = pos.x + ey; spy[my_off + 1] = pos.y + ey; spz[my_off + 1] = pos.z + ex;
+                spx[my_off + 2] = pos.x + ey; spy[my_off + 2] = pos.y + ex; spz[my_off + 2] = pos.z + ey;
+                spx[my_off + 3] = pos.x + ex; spy[my_off + 3] = pos.y + ex; spz[my_off + 3] = pos.z + ex;
+                // the sample the loop takes next if this candidate is culled: t += stepScale * distance
+                t_next = m.t + m.scale * m.dist_hit;
+                const V3 p = m.o + t_next * m.d;
+                spx[my_off + 4] = p.x; spy[my_off + 4] = p.y; spz[my_off + 4] = p.z;
             }
         }
-        const uint32_t idx = warp_take(q, refill_now<RMIN>(active) && !active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand && fetch_candidate_dyn(sc, wb, pq, TYPE, idx, s, shadow)) {
-            active = true; mode = 0; step = 0; t = s.lr.tmin; t_stop = s.lr.tcur;
+        __syncwarp();
+        for (uint32_t j = lane; j < total; j += 32u) sdist[j] = sdf_distance_dyn(SDF, v3(spx[j], spy[j], spz[j])); // the one evaluation site
+        __syncwarp();
+        if (m.active) {
+            bool have_sample = false;
+            float dist = 0.0f;
+            if (m.mode == 0) {
+                dist = sdist[my_off];
+                have_sample = true;
+            } else {
+                const float d0 = sdist[my_off + 0], d1 = sdist[my_off + 1], d2 = sdist[my_off + 2], d3 = sdist[my_off + 3];
+                evals += 4u;
+                const V3 acc = ((v3(ex, ey, ey) * v3s(d0) + v3(ey, ey, ex) * v3s(d1)) + v3(ey, ex, ey) * v3s(d2)) + v3(ex, ex, ex) * v3s(d3);
+                const V3 n = normalize(acc);
+                // IsAValidHit: in range and not back-facing
+                if (m.t >= 0.0f && m.t <= m.tcur && !(dot(m.d, n) > 0.0f)) {
+                    publish_lane_hit(sc, wb, TYPE, m, m.t, n);
+                    m.active = false;
+                } else {
+                    m.t = t_next;
+                    m.mode = 0;
+                    if (!(m.step < max_steps && m.t <= m.t_stop)) {
+                        wb.cand_res[TYPE][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+                        m.active = false;
+                    } else { dist = sdist[my_off + 4]; have_sample = true; }
+                }
+            }
+            if (have_sample) {
+                evals++;
+                m.step++;
+                if (dist <= threshold * m.t) { m.mode = 1; m.dist_hit = dist; }
+                else m.t += m.scale * dist;
+            }
         }
-        if (!__any_sync(kFull, active)) {
+        __syncwarp(); // the point list is rewritten by the next trip
+    }
+    return evals;
+}
+
+// ---- warp-private driver: lanes are refilled from the queue once RMIN of them idle -----------------
+template <int RMIN>
+__device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq,
+                                               int lane, CoopSmem& sm) {
+    const int TYPE = SDF + 3;
+    constexpr int kTrips = 8; // loop trips between refill checks
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
+    if (count == 0) return;
+    WarpChunk q;
+    MarchLane m;
+    m.active = false; m.mode = 0; m.step = 0; m.c = 0; m.r = 0; m.shadow = false;
+    m.o = v3s(0.0f); m.d = v3s(0.0f); m.t = m.tcur = m.t_stop = m.scale = m.dist_hit = 0.0f;
+    uint32_t work = 0;
+    for (;;) {
+        poll_committed(wb, TYPE, m);
+        const uint32_t idx = warp_take(q, refill_now<RMIN>(m.active) && !m.active, &ctrl->cursor[TYPE], count, lane);
+        if (idx != kNoCand) fetch_lane(sc, wb, pq, TYPE, idx, m);
+        if (!__any_sync(kFull, m.active)) {
             if (q.exhausted && q.next >= q.end) break;
             continue;
         }
-#pragma unroll 1
-        for (int trip = 0; trip < kTrips; trip++) {
-            // while (i++ < MaxSteps && t <= RayTCurrent())
-            if (active && mode == 0 && !(step < max_steps && t <= t_stop)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
-            const unsigned b1 = __ballot_sync(kFull, active && mode == 0), b5 = __ballot_sync(kFull, active && mode == 1);
-            if (!(b1 | b5)) break;
-            const uint32_t my_off = (uint32_t)__popc(b1 & lt) + 5u * (uint32_t)__popc(b5 & lt);
-            const uint32_t total = (uint32_t)__popc(b1) + 5u * (uint32_t)__popc(b5);
-            float t_next = 0.0f;
-            if (active) {
-                if (mode == 0) {
-                    const V3 p = s.lr.o + t * s.lr.d;
-                    spx[my_off] = p.x; spy[my_off] = p.y; spz[my_off] = p.z;
-                } else {
-                    spx[my_off + 0] = pos.x + ex; spy[my_off + 0] = pos.y + ey; spz[my_off + 0] = pos.z + ey;
-                    spx[my_off + 1] = pos.x + ey; spy[my_off + 1] = pos.y + ey; spz[my_off + 1] = pos.z + ex;
-                    spx[my_off + 2] = pos.x + ey; spy[my_off + 2] = pos.y + ex; spz[my_off + 2] = pos.z + ey;
-                    spx[my_off + 3] = pos.x + ex; spy[my_off + 3] = pos.y + ex; spz[my_off + 3] = pos.z + ex;
-                    // the sample the loop takes next if this candidate is culled: t += stepScale * distance
-                    t_next = t + s.step_scale * dist_hit;
-                    const V3 p = s.lr.o + t_next * s.lr.d;
-                    spx[my_off + 4] = p.x; spy[my_off + 4] = p.y; spz[my_off + 4] = p.z;
-                }
-            }
-            __syncwarp();
-            for (uint32_t j = lane; j < total; j += 32u) sdist[j] = sdf_distance_dyn(SDF, v3(spx[j], spy[j], spz[j])); // the one evaluation site
-            __syncwarp();
-            if (active) {
-                bool have_sample = false;
-                float dist = 0.0f;
-                if (mode == 0) {
-                    dist = sdist[my_off];
-                    have_sample = true;
-                } else {
-                    const float d0 = sdist[my_off + 0], d1 = sdist[my_off + 1], d2 = sdist[my_off + 2], d3 = sdist[my_off + 3];
-                    work += 4u;
-                    const V3 acc = ((v3(ex, ey, ey) * v3s(d0) + v3(ey, ey, ex) * v3s(d1)) + v3(ey, ex, ey) * v3s(d2)) + v3(ex, ex, ex) * v3s(d3);
-                    const V3 n = normalize(acc);
-                    if (is_valid_hit(s.lr, t, n)) {
-                        publish_hit_dyn(sc, wb, TYPE, s, t, n);
-                        active = false;
-                    } else {
-                        t = t_next;
-                        mode = 0;
-                        if (!(step < max_steps && t <= t_stop)) { wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); active = false; }
-                        else { dist = sdist[my_off + 4]; have_sample = true; }
-                    }
-                }
-                if (have_sample) {
-                    work++;
-                    step++;
-                    if (dist <= threshold * t) { mode = 1; pos = s.lr.o + t * s.lr.d; dist_hit = dist; }
-                    else t += s.step_scale * dist;
-                }
-            }
-            __syncwarp(); // the point list is rewritten by the next trip
-        }
+        work += coop_trips(SDF, m, kTrips, sc, pp, wb, lane, sm);
     }
     for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
     if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
 }
 
+// ---- block pool driver ---------------------------------------------------------------------------
+// Most queues of a 1080p wave hold fewer candidates than the machine has lanes, so a warp mostly
+// runs ONE batch of 32 rays to the end, and its cost is the step count of the slowest of them
+// (measured lane efficiency 0.5-0.6).  Here the 256 march states of a block are re-packed every
+// kTrips trips: live states move to the lowest thread indices (through shared memory), so live
+// rays always fill whole warps and warps without rays only wait at the barrier; free slots are
+// refilled with ONE atomicAdd per block.  Issue slots spent ~ sum(steps) / 32 instead of the sum
+// over warps of max(steps).
+struct PoolSmem {
+    float f[11][kBlock];          // o, d, tcur, t_stop, t, scale, dist_hit
+    uint32_t u[3][kBlock];        // c, r, step | mode << 16 | shadow << 17
+    uint32_t warp_cnt[kWarpsPerBlock];
+    uint32_t base;
+};
+
+__device__ __forceinline__ void pool_march_sdf(const int SDF, const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq,
+                                               CoopSmem& sm, PoolSmem& ps) {
+    const int TYPE = SDF + 3;
+    constexpr int kTrips = 8;
+    constexpr uint32_t kRefillMin = 64; // free slots that trigger a refill
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
+    if (count == 0) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    MarchLane m;
+    m.active = false; m.mode = 0; m.step = 0; m.c = 0; m.r = 0; m.shadow = false;
+    m.o = v3s(0.0f); m.d = v3s(0.0f); m.t = m.tcur = m.t_stop = m.scale = m.dist_hit = 0.0f;
+    uint32_t n_live = 0, work = 0; // n_live: states occupy threads [0, n_live) (some may have retired since the last packing)
+    bool exhausted = false;
+    for (;;) {
+        // (1) pack the live states to the front
+        {
+            const unsigned b = __ballot_sync(kFull, m.active);
+            if (lane == 0) ps.warp_cnt[warp] = (uint32_t)__popc(b);
+            __syncthreads();
+            uint32_t off = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarpsPerBlock; w++) {
+                const uint32_t c = ps.warp_cnt[w];
+                off += (w < warp) ? c : 0u;
+                total += c;
+            }
+            {
+                if (m.active) {
+                    const uint32_t slot = off + (uint32_t)__popc(b & ((1u << lane) - 1u));
+                    ps.f[0][slot] = m.o.x; ps.f[1][slot] = m.o.y; ps.f[2][slot] = m.o.z;
+                    ps.f[3][slot] = m.d.x; ps.f[4][slot] = m.d.y; ps.f[5][slot] = m.d.z;
+                    ps.f[6][slot] = m.tcur; ps.f[7][slot] = m.t_stop; ps.f[8][slot] = m.t; ps.f[9][slot] = m.scale; ps.f[10][slot] = m.dist_hit;
+                    ps.u[0][slot] = m.c; ps.u[1][slot] = m.r;
+                    ps.u[2][slot] = m.step | ((uint32_t)m.mode << 16) | ((m.shadow ? 1u : 0u) << 17);
+                }
+                __syncthreads();
+                m.active = (uint32_t)tid < total;
+                if (m.active) {
+                    m.o = v3(ps.f[0][tid], ps.f[1][tid], ps.f[2][tid]);
+                    m.d = v3(ps.f[3][tid], ps.f[4][tid], ps.f[5][tid]);
+                    m.tcur = ps.f[6][tid]; m.t_stop = ps.f[7][tid]; m.t = ps.f[8][tid]; m.scale = ps.f[9][tid]; m.dist_hit = ps.f[10][tid];
+                    m.c = ps.u[0][tid]; m.r = ps.u[1][tid];
+                    const uint32_t u = ps.u[2][tid];
+                    m.step = u & 0xFFFFu; m.mode = (int)((u >> 16) & 1u); m.shadow = ((u >> 17) & 1u) != 0u;
+                }
+            }
+            n_live = total;
+        }
+        // (2) refill the free slots from the type's queue
+        const uint32_t want = kBlock - n_live;
+        if (!exhausted && want >= kRefillMin) {
+            if (tid == 0) ps.base = atomicAdd(&ctrl->cursor[TYPE], want);
+            __syncthreads();
+            const uint32_t base = ps.base;
+            const uint32_t got = base < count ? min(want, count - base) : 0u;
+            if (got < want) exhausted = true;
+            if ((uint32_t)tid >= n_live && (uint32_t)tid < n_live + got) fetch_lane(sc, wb, pq, TYPE, base + ((uint32_t)tid - n_live), m);
+            n_live += got;
+        }
+        if (n_live == 0) {
+            if (exhausted) break;
+            continue;
+        }
+        // (3) march
+        poll_committed(wb, TYPE, m);
+        if (__any_sync(kFull, m.active)) work += coop_trips(SDF, m, kTrips, sc, pp, wb, lane, sm);
+    }
+    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
+    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Metaballs: step-parallel scan.
+// RayMetaballsIntersectionTest (src/VolumetricPrimitives.hlsli:151-202) is not a sphere tracer: it
+// samples the field at 128 FIXED steps t(i+1) = t(i) + dt, so all samples of a ray are known up
+// front.  One candidate per lane leaves most lanes idle (measured 10-13 of 32: three quarters of
+// the candidates cross no bounding sphere at all, the rest run 16..128 steps).  Here
+//   phase A  every lane takes a candidate, transforms the ray and runs FindIntersectingMetaballs;
+//            the survivors are appended to a warp-private list in shared memory,
+//   phase B  the warp walks the list one ray at a time, lane k sampling step (base + k); the first
+//            lane whose potential reaches the threshold gets its 6-tap normal from lanes 0..5, and
+//            IsAValidHit decides between ReportHit and going on with the next crossing.
+// Each lane accumulates t by the same repeated addition as the reference loop (k adds on top of
+// the pass's base), so every sample position -- and the parity build's result -- is bit-identical.
+// ---------------------------------------------------------------------------------------------
+template <int NB> __device__ __forceinline__ float metaballs_potential_masked(V3 p, const Metaballs<NB>& mb, uint32_t mask) {
+    float sum = 0.0f; // NB >= 5 builds sum over the balls whose bounding sphere the ray crosses, in index order
+#pragma unroll
+    for (int j = 0; j < NB; j++)
+        if (NB < 5 || ((mask >> j) & 1u)) sum += metaball_potential(p, mb.cx[j], mb.cy[j], mb.cz[j], mb.radius[j]);
+    return sum;
+}
+
+// FindIntersectingMetaballs (:124-147) without the in-place compaction: span + mask of crossed bounding spheres
+template <int NB>
+__device__ __forceinline__ uint32_t find_metaball_span(V3 o, V3 d, float ray_tmin, float ray_tcur, const Metaballs<NB>& mb, float& tmin, float& tmax) {
+    const float kInf = __builtin_inff();
+    LocalRay r;
+    r.o = o; r.d = d; r.tmin = ray_tmin; r.tcur = ray_tcur;
+    tmin = kInf;
+    tmax = -kInf;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int i = 0; i < NB; i++) {
+        float t0, t1;
+        if (ray_sphere_roots(r, v3(mb.cx[i], mb.cy[i], mb.cz[i]), mb.radius[i], t0, t1)) {
+            const float th = fmaxf(t0, r.tmin), tm = fminf(t1, r.tcur);
+            tmin = fminf(th, tmin);
+            tmax = fmaxf(tm, tmax);
+            mask |= 1u << i;
+        }
+    }
+    tmin = fmaxf(tmin, r.tmin);
+    tmax = fminf(tmax, r.tcur);
+    return mask;
+}
+
+template <int NB>
+__device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane,
+                                                     CoopSmem& sm) {
+    constexpr int TYPE = 2;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
+    if (count == 0) return;
+    const int warp = threadIdx.x >> 5;
+    // warp-private ray list, 12 words per entry, aliased onto the sphere tracer's point list (640 words per warp)
+    float* const L = sm.px[warp]; // px, py, pz, dist of one warp are NOT contiguous: use px/py/pz (3 x 160 words) as three 4-word-per-entry banks
+    float* const L1 = sm.py[warp];
+    float* const L2 = sm.pz[warp];
+    const uint32_t max_steps = pp.metaball_max_steps;
+    const float e = 0.5773f * 0.00001f;
+    Metaballs<NB> mb;
+    init_metaballs<NB>(mb, pp.fc.elapsed_time);
+    const unsigned lt = (1u << lane) - 1u;
+    WarpChunk q;
+    uint32_t work = 0;
+    for (;;) {
+        // ---- phase A: one candidate per lane ----
+        const uint32_t idx = warp_take(q, true, &ctrl->cursor[TYPE], count, lane);
+        bool keep = false;
+        MarchLane m;
+        float tmin = 0.0f, tmax = 0.0f;
+        uint32_t mask = 0;
+        if (idx != kNoCand && fetch_lane(sc, wb, pq, TYPE, idx, m)) {
+            mask = find_metaball_span<NB>(m.o, m.d, 0.0f, m.tcur, mb, tmin, tmax);
+            if (tmin == __builtin_inff()) wb.cand_res[TYPE][idx] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); // field is 0 at every sample
+            else keep = true;
+        }
+        const unsigned kb = __ballot_sync(kFull, keep);
+        const int n_list = __popc(kb);
+        if (keep) {
+            const int slot = __popc(kb & lt);
+            L[4 * slot + 0] = m.o.x; L[4 * slot + 1] = m.o.y; L[4 * slot + 2] = m.o.z; L[4 * slot + 3] = tmin;
+            L1[4 * slot + 0] = m.d.x; L1[4 * slot + 1] = m.d.y; L1[4 * slot + 2] = m.d.z;
+            L1[4 * slot + 3] = (tmax - tmin) / (float)(max_steps / 1u);
+            L2[4 * slot + 0] = m.tcur; L2[4 * slot + 1] = __uint_as_float(mask); L2[4 * slot + 2] = __uint_as_float(m.c);
+            L2[4 * slot + 3] = __uint_as_float(m.r);
+        }
+        __syncwarp();
+        // ---- phase B: one ray at a time, 32 steps per pass ----
+#pragma unroll 1
+        for (int ei = 0; ei < n_list; ei++) {
+            MarchLane r;
+            r.o = v3(L[4 * ei + 0], L[4 * ei + 1], L[4 * ei + 2]);
+            r.d = v3(L1[4 * ei + 0], L1[4 * ei + 1], L1[4 * ei + 2]);
+            float t_base = L[4 * ei + 3];
+            const float dt = L1[4 * ei + 3];
+            r.tcur = L2[4 * ei + 0];
+            const uint32_t bmask = __float_as_uint(L2[4 * ei + 1]);
+            r.c = __float_as_uint(L2[4 * ei + 2]);
+            r.r = __float_as_uint(L2[4 * ei + 3]);
+            bool done = false;
+            uint32_t steps_done = max_steps;
+#pragma unroll 1
+            for (uint32_t base = 0; base < max_steps && !done; base += 32u) {
+                // t of step (base + lane): the reference's `t += minTStep`, lane times
+                float t = t_base;
+                for (int k = 0; k < 31; k++) if (k < lane) t += dt;
+                const V3 p = r.o + t * r.d;
+                const float sum = metaballs_potential_masked<NB>(p, mb, bmask);
+                unsigned cross = __ballot_sync(kFull, sum >= 0.25f && base + (uint32_t)lane < max_steps);
+                while (cross) {
+                    const int k = __ffs(cross) - 1;
+                    cross &= cross - 1u;
+                    // CalculateMetaballsNormal at lane k's sample: taps -x +x -y +y -z +z on lanes 0..5
+                    const V3 pk = v3(__shfl_sync(kFull, p.x, k), __shfl_sync(kFull, p.y, k), __shfl_sync(kFull, p.z, k));
+                    const float tk = __shfl_sync(kFull, t, k);
+                    float f = 0.0f;
+                    if (lane < 6) {
+                        const float s = (lane & 1) ? e : -e;
+                        const V3 tap = v3(lane < 2 ? s : 0.0f, (lane >> 1) == 1 ? s : 0.0f, lane >= 4 ? s : 0.0f);
+                        f = metaballs_potential_masked<NB>(pk + tap, mb, bmask);
+                    }
+                    const float f0 = __shfl_sync(kFull, f, 0), f1 = __shfl_sync(kFull, f, 1), f2 = __shfl_sync(kFull, f, 2);
+                    const float f3 = __shfl_sync(kFull, f, 3), f4 = __shfl_sync(kFull, f, 4), f5 = __shfl_sync(kFull, f, 5);
+                    const V3 n = normalize(v3(f0 - f1, f2 - f3, f4 - f5));
+                    if (tk >= 0.0f && tk <= r.tcur && !(dot(r.d, n) > 0.0f)) { // IsAValidHit
+                        if (lane == 0) publish_lane_hit(sc, wb, TYPE, r, tk, n);
+                        steps_done = base + (uint32_t)k + 1u;
+                        done = true;
+                        break;
+                    }
+                }
+                // next pass starts one step after lane 31's sample
+                t_base = __shfl_sync(kFull, t, 31) + dt;
+            }
+            if (!done && lane == 0) wb.cand_res[TYPE][r.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+            work += steps_done;
+        }
+        __syncwarp();
+        if (q.exhausted && q.next >= q.end) break;
+    }
+    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
+}
+
 // ---- all types in one persistent launch ---------------------------------------------------------
 // The closed-form tests run first (they may occlude a shadow ray before its marches start).  The
-// marching types are then visited in an order ROTATED by the warp's global index, so all type
-// queues are drained concurrently from the start of the launch: the longest rays of different
-// types overlap instead of queueing behind one another.
+// marching types are then visited most expensive first -- pyramid, cog, metaballs, cylinders, mini
+// spheres, round cube, twisted torus, square torus -- but every SM starts at its own position of
+// that list (%smid) and wraps: all queues drain concurrently from the start of the launch, while
+// the warps resident on one SM run the same code (measured: with a per-warp rotation
+// stall_no_instruction became the top stall).  RMIN == 0 selects the block-pool driver.
 template <int NB, int RMIN>
 __global__ void __launch_bounds__(kBlock, 3) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                           const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
+                                                              const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
     __shared__ CoopSmem sm;
+    __shared__ PoolSmem ps;
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
     const int lane = threadIdx.x & 31;
     if (type_mask & (1u << 1)) analytic_queue<1>(sc, pp, wb, ctrl, pq, lane);
     if (type_mask & (1u << 0)) analytic_queue<0>(sc, pp, wb, ctrl, pq, lane);
-    // marching types, most expensive first: pyramid, cog, metaballs, cylinders, mini spheres, round cube,
-    // twisted torus, square torus (type ids).  Every SM starts at its own position of this list and
-    // wraps: all queues drain concurrently from the start of the launch, while the warps resident on
-    // one SM run the same code (the kernel is ~150 KB of SASS; mixed types on one SM thrash its
-    // instruction cache -- measured: stall_no_instruction was the top stall with a per-warp rotation).
     uint32_t rot;
     asm("mov.u32 %0, %%smid;" : "=r"(rot));
 #pragma unroll 1
     for (uint32_t i = 0; i < 8u; i++) {
         const int type = (int)((0x56438279u >> (4u * ((i + rot) & 7u))) & 15u);
         if (!((type_mask >> type) & 1u)) continue;
-        if (type == 2) simple_queue<2, NB>(sc, pp, wb, ctrl, pq, lane); // fixed-step scan: one candidate per lane measured fastest
-        else coop_march_sdf<RMIN>(type - 3, sc, pp, wb, ctrl, pq, lane, sm);
+        if (type == 2) scan_metaballs_queue<NB>(sc, pp, wb, ctrl, pq, lane, sm);
+        else if (RMIN == 0) pool_march_sdf(type - 3, sc, pp, wb, ctrl, pq, sm, ps);
+        else coop_march_sdf<(RMIN ? RMIN : 1)>(type - 3, sc, pp, wb, ctrl, pq, lane, sm);
     }
 }
 
@@ -225,7 +487,9 @@ template <int SDF, int RMIN>
 __global__ void __launch_bounds__(kBlock) k_coop_sdf(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                      const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ CoopSmem sm;
-    coop_march_sdf<RMIN>(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
+    __shared__ PoolSmem ps;
+    if (RMIN == 0) pool_march_sdf(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, sm, ps);
+    else coop_march_sdf<(RMIN ? RMIN : 1)>(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
 }
 
 } // namespace

@@ -27,12 +27,71 @@ Renderer::Renderer(int scene_id, uint32_t width, uint32_t height, uint32_t grid_
 Renderer::~Renderer() { on_destroy(); }
 
 void Renderer::on_destroy() {
+    for (int i = 1; i < kFrameCount; i++)
+        if (m_frame_ctx[i]) { gprt_sync(m_frame_ctx[i]); gprt_destroy(m_frame_ctx[i]); m_frame_ctx[i] = nullptr; }
+    m_frame_ctx[0] = nullptr;
     if (m_ctx) {
         gprt_sync(m_ctx);
         gprt_destroy(m_ctx);
         m_ctx = nullptr;
     }
     m_initialized = false;
+}
+
+// Frame slots 1..2 are created on first use: same geometry, shader table and (deterministic) LBVH.
+int Renderer::ensure_frame_contexts() {
+    if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
+    m_frame_ctx[0] = m_ctx;
+    for (int i = 1; i < kFrameCount; i++) {
+        if (m_frame_ctx[i]) continue;
+        gprt_ctx* saved = m_ctx;
+        int rc = gprt_create(&m_ctx, m_device, &m_scene.config);
+        if (rc == GPRT_OK) rc = create_device_dependent_resources();
+        gprt_ctx* made = m_ctx;
+        m_ctx = saved;
+        if (rc != GPRT_OK) { if (made) gprt_destroy(made); return rc; }
+        m_frame_ctx[i] = made;
+    }
+    return GPRT_OK;
+}
+
+int Renderer::on_render_async(void* h_rgba8_pinned) {
+    int rc = ensure_frame_contexts();
+    if (rc != GPRT_OK) return rc;
+    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    m_frame_index++;
+    rc = gprt_sync(c); // this slot's previous frame (its staging, queues and host buffer) must be done
+    if (rc != GPRT_OK) return rc;
+    const gprt_rect tile = {0, 0, m_scene.width, m_scene.height};
+    m_last_tile = tile;
+    return gprt_dispatch_host_async(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
+                                    m_scene.height, tile, h_rgba8_pinned, (size_t)tile.w * 4, nullptr);
+}
+
+int Renderer::do_raytracing_async(void* d_rgba8) {
+    int rc = ensure_frame_contexts();
+    if (rc != GPRT_OK) return rc;
+    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    m_frame_index++;
+    rc = gprt_sync(c);
+    if (rc != GPRT_OK) return rc;
+    const gprt_rect tile = {0, 0, m_scene.width, m_scene.height};
+    m_last_tile = tile;
+    return gprt_dispatch(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width, m_scene.height,
+                         tile, d_rgba8, (size_t)tile.w * 4, nullptr, nullptr);
+}
+
+int Renderer::wait_for_gpu() {
+    int rc = GPRT_OK;
+    if (m_ctx) rc = gprt_sync(m_ctx);
+    for (int i = 1; i < kFrameCount; i++)
+        if (m_frame_ctx[i]) { const int r2 = gprt_sync(m_frame_ctx[i]); if (rc == GPRT_OK) rc = r2; }
+    return rc;
+}
+
+gprt_ctx* Renderer::frame_context(int slot) {
+    if (slot < 0 || slot >= kFrameCount) return nullptr;
+    return slot == 0 ? m_ctx : m_frame_ctx[slot];
 }
 
 int Renderer::on_init() {
@@ -156,6 +215,10 @@ int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, 
                                         uint32_t* d_hit_ids) {
     return r ? r->impl.do_raytracing_stripes(stripe_rows, rank, world, d_rgba8, d_hit_ids) : GPRT_E_INVALID_ARG;
 }
+int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned) { return r ? r->impl.on_render_async(h_rgba8_pinned) : GPRT_E_INVALID_ARG; }
+int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8) { return r ? r->impl.do_raytracing_async(d_rgba8) : GPRT_E_INVALID_ARG; }
+int gprt_renderer_wait_for_gpu(gprt_renderer* r) { return r ? r->impl.wait_for_gpu() : GPRT_E_INVALID_ARG; }
+gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot) { return r ? r->impl.frame_context(slot) : nullptr; }
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t w, uint32_t h) {
     return r ? r->impl.on_size_changed(w, h) : GPRT_E_INVALID_ARG;
 }

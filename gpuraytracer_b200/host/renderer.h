@@ -23,6 +23,14 @@ public:
     int do_raytracing(gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, float* d_rgba_f32); // :401-452
     // multi-GPU: this rank's row stripes only (gprt_dispatch_stripes), packed output
     int do_raytracing_stripes(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8, uint32_t* d_hit_ids);
+    // Frames in flight (src/Renderer.h:92 frame_count = 3, DeviceResources::move_to_next_frame): frame k
+    // is rendered by context k % 3 on that context's own stream, so the tail of one frame (a few long
+    // rays) overlaps the bulk of the next and the copy to the host overlaps rendering.  Each call
+    // first waits for the slot's previous frame, like the reference waits on its frame fence.
+    int on_render_async(void* h_rgba8_pinned);                   // on_render, 3 frames in flight, whole image
+    int do_raytracing_async(void* d_rgba8);                      // same with device output
+    int wait_for_gpu();                                          // DeviceResources::wait_for_gpu: all frames done
+    gprt_ctx* frame_context(int slot);
     float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399
 
     SceneState& scene() { return m_scene; }
@@ -36,7 +44,11 @@ private:
     int build_acceleration_structures();       // :788-835  -> gprt_build_accel
 
     SceneState m_scene;
-    gprt_ctx* m_ctx = nullptr;
+    static constexpr int kFrameCount = 3;
+    int ensure_frame_contexts();
+    gprt_ctx* m_ctx = nullptr;           // frame slot 0 (and the synchronous path)
+    gprt_ctx* m_frame_ctx[kFrameCount] = {nullptr, nullptr, nullptr};
+    uint32_t m_frame_index = 0;
     int m_device = -1;
     bool m_valid = false;
     bool m_initialized = false;

@@ -84,6 +84,22 @@ class Renderer:
         check(self._lib.gprt_renderer_do_raytracing_stripes(self._h, int(stripe_rows), int(rank), int(world), d_rgba8_ptr, d_hit_ids_ptr),
               "do_raytracing_stripes")
 
+    def on_render_async(self, h_rgba8_ptr):
+        """on_render with 3 frames in flight: enqueue this frame (host output, pinned memory) and return."""
+        check(self._lib.gprt_renderer_on_render_async(self._h, h_rgba8_ptr), "on_render_async")
+
+    def do_raytracing_async(self, d_rgba8_ptr):
+        """do_raytracing with 3 frames in flight (device output)."""
+        check(self._lib.gprt_renderer_do_raytracing_async(self._h, d_rgba8_ptr), "do_raytracing_async")
+
+    def wait_for_gpu(self):
+        check(self._lib.gprt_renderer_wait_for_gpu(self._h), "wait_for_gpu")
+
+    def frame_stream(self, slot):
+        """cudaStream_t (int) of frame slot `slot`, or 0 if the slot has not been used yet."""
+        ctx = self._lib.gprt_renderer_frame_context(self._h, int(slot))
+        return int(self._lib.gprt_get_stream(ctx) or 0) if ctx else 0
+
     def sync(self):
         check(self._lib.gprt_sync(self.context), "sync")
 

@@ -258,6 +258,17 @@ int gprt_dispatch_stripes(gprt_ctx* ctx, const gprt_scene_cb* scene,
                           void* d_rgba8, size_t pitch_bytes, uint32_t* d_hit_ids);
 uint32_t gprt_stripe_local_rows(uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t world);
 
+/* gprt_dispatch_host without the final wait: the copy to h_rgba8 (pinned memory for a truly
+ * asynchronous copy) is enqueued on the context stream and the call returns; gprt_sync() completes
+ * it.  With one context per frame in flight this is the reference's frame pipelining
+ * (frame_count = 3, src/Renderer.h:92; DeviceResources::move_to_next_frame). */
+int gprt_dispatch_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
+                             const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
+                             uint32_t width, uint32_t height, gprt_rect tile,
+                             void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids);
+/* The context's CUDA stream (cudaStream_t as void*). */
+void* gprt_get_stream(gprt_ctx* ctx);
+
 #define GPRT_HIT_MISS     0xFFFFFFFFu
 #define GPRT_HIT_TRIANGLE 0x00000000u /* | PrimitiveIndex()  (instance 0)               */
 #define GPRT_HIT_AABB     0x10000000u /* | GeometryIndex     (instance 1)               */

@@ -60,6 +60,13 @@ int gprt_renderer_do_raytracing(gprt_renderer* r, gprt_rect tile, void* d_rgba8,
  * gprt_stripe_local_rows() packed rows of width * 4 bytes in device memory; asynchronous. */
 int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world,
                                         void* d_rgba8, uint32_t* d_hit_ids);
+/* Frames in flight (frame_count = 3, src/Renderer.h:92): frame k is rendered by context k % 3 on its
+ * own stream; each call first waits for that slot's previous frame.  h_rgba8_pinned / d_rgba8 must
+ * stay valid until gprt_renderer_wait_for_gpu (or until the slot comes round again). */
+int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned);
+int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8);
+int gprt_renderer_wait_for_gpu(gprt_renderer* r);
+gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot); /* NULL until the slot was used */
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);
 
 int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out);

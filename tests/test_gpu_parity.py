@@ -178,6 +178,33 @@ def test_deterministic_and_reusable_context():
         assert r.primary_mrays_per_s() > 0
 
 
+def test_frames_in_flight_equal_synchronous_frames():
+    """on_render_async (3 contexts, 3 streams, frame k on slot k % 3) returns the same frames as on_render."""
+    import torch
+    times = [0.1 * k for k in range(7)]
+    with Renderer(scene_id=0, width=320, height=180, device=0, config=make_cfg()) as r:
+        r.on_init()
+        ref = []
+        for t in times:
+            r.on_update(t)
+            ref.append(r.on_render()[0].copy())
+        host = [torch.zeros((180, 320, 4), dtype=torch.uint8).pin_memory() for _ in times]
+        for t, h in zip(times, host):
+            r.on_update(t)
+            r.on_render_async(h.data_ptr())
+        r.wait_for_gpu()
+        assert len({r.frame_stream(s) for s in range(3)}) == 3 and r.frame_stream(1) != 0
+        for a, h in zip(ref, host):
+            np.testing.assert_array_equal(a, h.numpy())
+        dev = [torch.zeros((180, 320, 4), dtype=torch.uint8, device="cuda") for _ in times]
+        for t, d in zip(times, dev):
+            r.on_update(t)
+            r.do_raytracing_async(d.data_ptr())
+        r.wait_for_gpu()
+        for a, d in zip(ref, dev):
+            np.testing.assert_array_equal(a, d.cpu().numpy())
+
+
 def test_internal_banding_is_invisible():
     """A frame larger than the internal pass size is rendered in bands; compare against tiles."""
     with Renderer(scene_id=0, width=2560, height=1800, device=0, config=make_cfg()) as r:  # 4.6 Mpx > 2^22
