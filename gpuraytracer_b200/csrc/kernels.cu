@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ 
 } // namespace
 } // namespace gprt
 
-#include "march.cuh" // k_march_sdf / k_march_metaballs (same anonymous namespace)
+#include "march.cuh" // queue plumbing, analytic tests (same anonymous namespace)
 #include "march_coop.cuh" // k_intersect_coop: warp-cooperative sphere tracer (the production path)
 
 namespace gprt {
@@ -386,14 +386,15 @@ int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers&
     return 1;
 }
 
-// GPRT_ISECT_VARIANT (A/B aid): unset or 200+R = warp-cooperative marchers refilling once R lanes idle
-// (the production path, R = 8); -1 = one candidate per lane to completion; 16 = per-lane state
-// machines with refill (march.cuh).
-int isect_variant() {
+// GPRT_ISECT_VARIANT=-1 (profiling aid): with GPRT_PER_TYPE_LAUNCHES=1, run the one-candidate-per-thread kernels, which
+// also fill the per-candidate cost statistics of gprt_get_wave_stats.  Otherwise: the production kernels.
+bool stats_kernels() {
     static int v = -1000;
-    if (v == -1000) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 208; }
-    return v;
+    if (v == -1000) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 0; }
+    return v == -1;
 }
+
+constexpr int kRefillMin = 8; // idle lanes of a warp that trigger a refill from the queue (measured: 1, 8, 16, 24 within 3 %)
 
 template <class K> int persistent_grid(K kernel) {
     int per_sm = 0;
@@ -402,23 +403,21 @@ template <class K> int persistent_grid(K kernel) {
     return sm_count() * per_sm;
 }
 
+// one launch per primitive type (GPRT_PER_TYPE_LAUNCHES=1: per-type device times)
 template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
     if constexpr (TYPE >= 3) {
-        if (isect_variant() >= 200) {
-            static const int grid = persistent_grid(k_coop_sdf<TYPE - 3, 8>);
-            k_coop_sdf<TYPE - 3, 8><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+        if (!stats_kernels()) {
+            static const int grid = persistent_grid(k_coop_sdf<TYPE - 3, kRefillMin>);
+            k_coop_sdf<TYPE - 3, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
             return;
         }
     }
-    if (TYPE >= 2 && isect_variant() > 0) {
-        if (TYPE == 2) {
-            static const int grid = persistent_grid(k_march_metaballs<NB>);
-            k_march_metaballs<NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
-        } else {
-            static const int grid = persistent_grid(k_march_sdf<(TYPE >= 3 ? TYPE - 3 : 0)>);
-            k_march_sdf<(TYPE >= 3 ? TYPE - 3 : 0)><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+    if constexpr (TYPE == 2) {
+        if (!stats_kernels()) {
+            static const int grid = persistent_grid(k_scan_metaballs<NB>);
+            k_scan_metaballs<NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+            return;
         }
-        return;
     }
     static const int grid = persistent_grid(k_intersect<TYPE, NB>);
     k_intersect<TYPE, NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
@@ -445,25 +444,14 @@ int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers
     return 1;
 }
 
-template <int NB, int RMIN> void launch_all_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
-    static const int grid = persistent_grid(k_intersect_all<NB, RMIN>);
-    k_intersect_all<NB, RMIN><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
-}
-template <int NB, int RMIN> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
-    static const int grid = persistent_grid(k_intersect_coop<NB, RMIN>);
-    k_intersect_coop<NB, RMIN><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
-}
-template <int NB> void launch_all_v(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
-    switch (isect_variant()) {
-    case -1: launch_all_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
-    case 16: launch_all_t<NB, 16>(sc, pp, wb, wave, type_mask, s); break;
-    case 200: launch_coop_t<NB, 0>(sc, pp, wb, wave, type_mask, s); break;
-    default: launch_coop_t<NB, 8>(sc, pp, wb, wave, type_mask, s); break;
-    }
+// the production path: every primitive type in one persistent launch per wave
+template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
+    static const int grid = persistent_grid(k_intersect_coop<NB, kRefillMin>);
+    k_intersect_coop<NB, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
 int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {
-    if (metaballs == 5) launch_all_v<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
-    else launch_all_v<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+    if (metaballs == 5) launch_coop_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+    else launch_coop_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
     return 1;
 }
 

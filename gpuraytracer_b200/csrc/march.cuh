@@ -1,17 +1,7 @@
-// march.cuh -- warp-coherent ray marchers with lane refill (included by kernels.cu).
-//
-// The reference's sphere tracer (RaySignedDistancePrimitiveTest, src/SignedDistancePrimitives.hlsli:
-// 287-319) and metaball marcher (RayMetaballsIntersectionTest, src/VolumetricPrimitives.hlsli:
-// 151-202) take anything between 1 and 512 (128) iterations per ray.  One-candidate-per-thread
-// leaves most lanes of a warp idle while the slowest lane finishes.  Here every lane is a small
-// state machine and the expensive field evaluation is a single, convergent call site per loop
-// trip:
-//   mode 0        march:   p = o + t d, evaluate the field, test the hit criterion
-//   mode 1..TAPS  normal:  evaluate the field at the k-th finite-difference tap (the reference
-//                 computes the normal inside the loop because IsAValidHit culls on it)
-// A lane that finishes (hit, cull-and-continue exhausted, or ray end) publishes its result and is
-// refilled from a warp-private chunk of the type's candidate queue; chunks come from one global
-// atomic per kChunk candidates.  Arithmetic (and so the parity build's bits) is unchanged.
+// march.cuh -- candidate-queue plumbing shared by the intersection kernels (included by kernels.cu):
+// warp-aggregated queue reservation (warp_take), GetRayInAABBPrimitiveLocalSpace for one queue entry
+// (fetch_candidate), ReportHit (publish_hit), the closed-form analytic tests over their queues and the
+// one-candidate-per-lane baseline marcher (simple_queue).  The production marchers are in march_coop.cuh.
 #pragma once
 
 namespace gprt {
@@ -102,146 +92,6 @@ template <int TYPE> __device__ __forceinline__ void publish_miss(const WaveBuffe
     wb.cand_res[TYPE][s.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
 }
 
-// ---------------------------------------------------------------------------------------------
-// Sphere tracer for SDF type SDF (0..6); queue / kernel type id is SDF + 3.
-// ---------------------------------------------------------------------------------------------
-template <int SDF, int RMIN>
-__device__ __forceinline__ void march_sdf_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
-    constexpr int TYPE = SDF + 3;
-    constexpr int kTrips = (SDF == 6) ? 4 : 8; // loop trips between refill checks
-    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
-    const uint32_t max_steps = pp.sdf_max_steps;
-    const float threshold = 0.0001f;
-    // tetrahedral taps of sdCalculateNormal: e.xyy, e.yyx, e.yxy, e.xxx
-    const float ex = 1.0f * 0.5773f * 0.0001f, ey = -1.0f * 0.5773f * 0.0001f;
-
-    WarpChunk q;
-    CandState s;
-    bool active = false;
-    int mode = 0;
-    uint32_t step = 0, work = 0;
-    float t = 0.0f, dist_hit = 0.0f;
-    V3 pos = v3s(0.0f), acc = v3s(0.0f);
-
-    for (;;) {
-        const uint32_t idx = warp_take(q, refill_now<RMIN>(active) && !active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand && fetch_candidate<TYPE>(sc, wb, pq, idx, s)) {
-            active = true; mode = 0; step = 0; t = s.lr.tmin;
-        }
-        if (!__any_sync(kFull, active)) {
-            if (q.exhausted && q.next >= q.end) break;
-            continue;
-        }
-#pragma unroll 1
-        for (int trip = 0; trip < kTrips; trip++) {
-            // while (i++ < MaxSteps && t <= RayTCurrent())
-            if (active && mode == 0 && !(step < max_steps && t <= s.lr.tcur)) { publish_miss<TYPE>(wb, s); active = false; }
-            if (active) {
-                V3 tap = v3s(0.0f);
-                if (mode == 1) tap = v3(ex, ey, ey);
-                else if (mode == 2) tap = v3(ey, ey, ex);
-                else if (mode == 3) tap = v3(ey, ex, ey);
-                else if (mode == 4) tap = v3(ex, ex, ex);
-                const V3 p = (mode == 0) ? s.lr.o + t * s.lr.d : pos + tap;
-                const float dist = sdf_distance<SDF>(p); // the one convergent evaluation site
-                work++;
-                if (mode == 0) {
-                    step++;
-                    if (dist <= threshold * t) { mode = 1; pos = p; dist_hit = dist; }
-                    else t += s.step_scale * dist;
-                } else {
-                    const V3 term = tap * v3s(dist);
-                    acc = (mode == 1) ? term : acc + term;
-                    if (mode == 4) {
-                        const V3 n = normalize(acc);
-                        if (is_valid_hit(s.lr, t, n)) { publish_hit<TYPE>(sc, wb, s, t, n); active = false; }
-                        else { t += s.step_scale * dist_hit; mode = 0; }
-                    } else {
-                        mode++;
-                    }
-                }
-            }
-        }
-    }
-    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
-    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
-}
-
-// ---------------------------------------------------------------------------------------------
-// Metaball marcher (type id 2): fixed step, 6 central-difference taps for the normal.
-// ---------------------------------------------------------------------------------------------
-template <int NB, int RMIN>
-__device__ __forceinline__ void march_metaballs_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
-    constexpr int TYPE = 2;
-    constexpr int kTrips = 8;
-    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
-    const uint32_t max_steps = pp.metaball_max_steps;
-    const float e = 0.5773f * 0.00001f;
-
-    WarpChunk q;
-    CandState s;
-    Metaballs<NB> mb;
-    bool active = false;
-    int mode = 0;
-    uint32_t step = 0, work = 0;
-    float t = 0.0f, t_step = 0.0f, prev = 0.0f;
-    V3 pos = v3s(0.0f), nrm = v3s(0.0f);
-
-    for (;;) {
-        const uint32_t idx = warp_take(q, refill_now<RMIN>(active) && !active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand && fetch_candidate<TYPE>(sc, wb, pq, idx, s)) {
-            init_metaballs<NB>(mb, pp.fc.elapsed_time);
-            float tmin, tmax;
-            find_intersecting_metaballs<NB>(s.lr, mb, tmin, tmax);
-            if (tmin == __builtin_inff()) {
-                publish_miss<TYPE>(wb, s); // no bounding sphere crossed: the field is 0 at every sample
-            } else {
-                active = true; mode = 0; step = 0; t = tmin;
-                t_step = (tmax - tmin) / (float)(max_steps / 1u);
-            }
-        }
-        if (!__any_sync(kFull, active)) {
-            if (q.exhausted && q.next >= q.end) break;
-            continue;
-        }
-#pragma unroll 1
-        for (int trip = 0; trip < kTrips; trip++) {
-            if (active && mode == 0 && !(step < max_steps)) { publish_miss<TYPE>(wb, s); active = false; }
-            if (active) {
-                V3 tap = v3s(0.0f);
-                if (mode == 1) tap = v3(-e, 0, 0);
-                else if (mode == 2) tap = v3(e, 0, 0);
-                else if (mode == 3) tap = v3(0, -e, 0);
-                else if (mode == 4) tap = v3(0, e, 0);
-                else if (mode == 5) tap = v3(0, 0, -e);
-                else if (mode == 6) tap = v3(0, 0, e);
-                const V3 p = (mode == 0) ? s.lr.o + t * s.lr.d : pos + tap;
-                const float sum = metaballs_potential<NB>(p, mb); // the one convergent evaluation site
-                if (mode == 0) {
-                    step++;
-                    work++;
-                    if (sum >= 0.25f) { mode = 1; pos = p; }
-                    else t += t_step;
-                } else {
-                    if (mode & 1) prev = sum;
-                    else if (mode == 2) nrm.x = prev - sum;
-                    else if (mode == 4) nrm.y = prev - sum;
-                    else nrm.z = prev - sum;
-                    if (mode == 6) {
-                        const V3 n = normalize(nrm);
-                        if (is_valid_hit(s.lr, t, n)) { publish_hit<TYPE>(sc, wb, s, t, n); active = false; }
-                        else { t += t_step; mode = 0; }
-                    } else {
-                        mode++;
-                    }
-                }
-            }
-        }
-    }
-    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
-    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
-}
-
 // Analytic types (0 box, 1 spheres): one cheap closed-form test per candidate, no state machine.
 template <int TYPE>
 __device__ __forceinline__ void analytic_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
@@ -266,18 +116,6 @@ __device__ __forceinline__ void analytic_queue(const SceneDev& sc, const PassPar
     if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
 }
 
-// ---- one kernel per type (profiling mode: per-type device times) -------------------------------
-template <int SDF>
-__global__ void __launch_bounds__(kBlock) k_march_sdf(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                      const __grid_constant__ WaveBuffers wb, int wave) {
-    march_sdf_queue<SDF, 1>(sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31);
-}
-template <int NB>
-__global__ void __launch_bounds__(kBlock) k_march_metaballs(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                            const __grid_constant__ WaveBuffers wb, int wave) {
-    march_metaballs_queue<NB, 1>(sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31);
-}
-
 // One candidate per lane, run to completion, then the warp takes the next 32 (no state machine).
 template <int TYPE, int NB>
 __device__ __forceinline__ void simple_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
@@ -300,38 +138,6 @@ __device__ __forceinline__ void simple_queue(const SceneDev& sc, const PassParam
     }
     for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
     if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
-}
-
-// ---- all types in one persistent launch ---------------------------------------------------------
-// Every warp works through the type queues in a fixed order, most expensive first (longest
-// processing time first): while the last long pyramid rays finish, the other warps are already
-// draining the cheaper queues, so no SM idles in a per-type tail and a wave costs one launch
-// instead of ten.  RMIN: refill threshold of the marchers; RMIN == 0 selects simple_queue.
-template <int SDF, int NB, int RMIN>
-__device__ __forceinline__ void sdf_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
-    if (RMIN == 0) simple_queue<SDF + 3, NB>(sc, pp, wb, ctrl, pq, lane);
-    else march_sdf_queue<SDF, (RMIN ? RMIN : 1)>(sc, pp, wb, ctrl, pq, lane);
-}
-template <int NB, int RMIN>
-__global__ void __launch_bounds__(kBlock) k_intersect_all(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                          const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
-    WaveCtrl* ctrl = &wb.ctrl[wave];
-    const int pq = wave & 1;
-    const int lane = threadIdx.x & 31;
-    // the closed-form tests cost next to nothing and may occlude a shadow ray before its marches start
-    if (type_mask & (1u << 1)) analytic_queue<1>(sc, pp, wb, ctrl, pq, lane);
-    if (type_mask & (1u << 0)) analytic_queue<0>(sc, pp, wb, ctrl, pq, lane);
-    if (type_mask & (1u << 9)) sdf_queue<6, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // fractal pyramid
-    if (type_mask & (1u << 7)) sdf_queue<4, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // cog
-    if (type_mask & (1u << 2)) {
-        if (RMIN == 0) simple_queue<2, NB>(sc, pp, wb, ctrl, pq, lane);
-        else march_metaballs_queue<NB, (RMIN ? RMIN : 1)>(sc, pp, wb, ctrl, pq, lane);
-    }
-    if (type_mask & (1u << 8)) sdf_queue<5, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // cylinders
-    if (type_mask & (1u << 3)) sdf_queue<0, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // mini spheres
-    if (type_mask & (1u << 4)) sdf_queue<1, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // intersected round cube
-    if (type_mask & (1u << 6)) sdf_queue<3, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // twisted torus
-    if (type_mask & (1u << 5)) sdf_queue<2, NB, RMIN>(sc, pp, wb, ctrl, pq, lane); // square torus
 }
 
 } // namespace

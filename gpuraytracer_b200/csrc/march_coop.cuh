@@ -224,92 +224,6 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
     if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
 }
 
-// ---- block pool driver ---------------------------------------------------------------------------
-// Most queues of a 1080p wave hold fewer candidates than the machine has lanes, so a warp mostly
-// runs ONE batch of 32 rays to the end, and its cost is the step count of the slowest of them
-// (measured lane efficiency 0.5-0.6).  Here the 256 march states of a block are re-packed every
-// kTrips trips: live states move to the lowest thread indices (through shared memory), so live
-// rays always fill whole warps and warps without rays only wait at the barrier; free slots are
-// refilled with ONE atomicAdd per block.  Issue slots spent ~ sum(steps) / 32 instead of the sum
-// over warps of max(steps).
-struct PoolSmem {
-    float f[11][kBlock];          // o, d, tcur, t_stop, t, scale, dist_hit
-    uint32_t u[3][kBlock];        // c, r, step | mode << 16 | shadow << 17
-    uint32_t warp_cnt[kWarpsPerBlock];
-    uint32_t base;
-};
-
-__device__ __forceinline__ void pool_march_sdf(const int SDF, const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq,
-                                               CoopSmem& sm, PoolSmem& ps) {
-    const int TYPE = SDF + 3;
-    constexpr int kTrips = 8;
-    constexpr uint32_t kRefillMin = 64; // free slots that trigger a refill
-    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
-    if (count == 0) return;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    MarchLane m;
-    m.active = false; m.mode = 0; m.step = 0; m.c = 0; m.r = 0; m.shadow = false;
-    m.o = v3s(0.0f); m.d = v3s(0.0f); m.t = m.tcur = m.t_stop = m.scale = m.dist_hit = 0.0f;
-    uint32_t n_live = 0, work = 0; // n_live: states occupy threads [0, n_live) (some may have retired since the last packing)
-    bool exhausted = false;
-    for (;;) {
-        // (1) pack the live states to the front
-        {
-            const unsigned b = __ballot_sync(kFull, m.active);
-            if (lane == 0) ps.warp_cnt[warp] = (uint32_t)__popc(b);
-            __syncthreads();
-            uint32_t off = 0, total = 0;
-#pragma unroll
-            for (int w = 0; w < kWarpsPerBlock; w++) {
-                const uint32_t c = ps.warp_cnt[w];
-                off += (w < warp) ? c : 0u;
-                total += c;
-            }
-            {
-                if (m.active) {
-                    const uint32_t slot = off + (uint32_t)__popc(b & ((1u << lane) - 1u));
-                    ps.f[0][slot] = m.o.x; ps.f[1][slot] = m.o.y; ps.f[2][slot] = m.o.z;
-                    ps.f[3][slot] = m.d.x; ps.f[4][slot] = m.d.y; ps.f[5][slot] = m.d.z;
-                    ps.f[6][slot] = m.tcur; ps.f[7][slot] = m.t_stop; ps.f[8][slot] = m.t; ps.f[9][slot] = m.scale; ps.f[10][slot] = m.dist_hit;
-                    ps.u[0][slot] = m.c; ps.u[1][slot] = m.r;
-                    ps.u[2][slot] = m.step | ((uint32_t)m.mode << 16) | ((m.shadow ? 1u : 0u) << 17);
-                }
-                __syncthreads();
-                m.active = (uint32_t)tid < total;
-                if (m.active) {
-                    m.o = v3(ps.f[0][tid], ps.f[1][tid], ps.f[2][tid]);
-                    m.d = v3(ps.f[3][tid], ps.f[4][tid], ps.f[5][tid]);
-                    m.tcur = ps.f[6][tid]; m.t_stop = ps.f[7][tid]; m.t = ps.f[8][tid]; m.scale = ps.f[9][tid]; m.dist_hit = ps.f[10][tid];
-                    m.c = ps.u[0][tid]; m.r = ps.u[1][tid];
-                    const uint32_t u = ps.u[2][tid];
-                    m.step = u & 0xFFFFu; m.mode = (int)((u >> 16) & 1u); m.shadow = ((u >> 17) & 1u) != 0u;
-                }
-            }
-            n_live = total;
-        }
-        // (2) refill the free slots from the type's queue
-        const uint32_t want = kBlock - n_live;
-        if (!exhausted && want >= kRefillMin) {
-            if (tid == 0) ps.base = atomicAdd(&ctrl->cursor[TYPE], want);
-            __syncthreads();
-            const uint32_t base = ps.base;
-            const uint32_t got = base < count ? min(want, count - base) : 0u;
-            if (got < want) exhausted = true;
-            if ((uint32_t)tid >= n_live && (uint32_t)tid < n_live + got) fetch_lane(sc, wb, pq, TYPE, base + ((uint32_t)tid - n_live), m);
-            n_live += got;
-        }
-        if (n_live == 0) {
-            if (exhausted) break;
-            continue;
-        }
-        // (3) march
-        poll_committed(wb, TYPE, m);
-        if (__any_sync(kFull, m.active)) work += coop_trips(SDF, m, kTrips, sc, pp, wb, lane, sm);
-    }
-    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
-    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
-}
-
 // ---------------------------------------------------------------------------------------------
 // Metaballs: step-parallel scan.
 // RayMetaballsIntersectionTest (src/VolumetricPrimitives.hlsli:151-202) is not a sphere tracer: it
@@ -459,12 +373,11 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
 // spheres, round cube, twisted torus, square torus -- but every SM starts at its own position of
 // that list (%smid) and wraps: all queues drain concurrently from the start of the launch, while
 // the warps resident on one SM run the same code (measured: with a per-warp rotation
-// stall_no_instruction became the top stall).  RMIN == 0 selects the block-pool driver.
+// stall_no_instruction became the top stall).
 template <int NB, int RMIN>
 __global__ void __launch_bounds__(kBlock, 3) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
     __shared__ CoopSmem sm;
-    __shared__ PoolSmem ps;
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
     const int lane = threadIdx.x & 31;
@@ -477,8 +390,7 @@ __global__ void __launch_bounds__(kBlock, 3) k_intersect_coop(const __grid_const
         const int type = (int)((0x56438279u >> (4u * ((i + rot) & 7u))) & 15u);
         if (!((type_mask >> type) & 1u)) continue;
         if (type == 2) scan_metaballs_queue<NB>(sc, pp, wb, ctrl, pq, lane, sm);
-        else if (RMIN == 0) pool_march_sdf(type - 3, sc, pp, wb, ctrl, pq, sm, ps);
-        else coop_march_sdf<(RMIN ? RMIN : 1)>(type - 3, sc, pp, wb, ctrl, pq, lane, sm);
+        else coop_march_sdf<RMIN>(type - 3, sc, pp, wb, ctrl, pq, lane, sm);
     }
 }
 
@@ -487,9 +399,14 @@ template <int SDF, int RMIN>
 __global__ void __launch_bounds__(kBlock) k_coop_sdf(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                      const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ CoopSmem sm;
-    __shared__ PoolSmem ps;
-    if (RMIN == 0) pool_march_sdf(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, sm, ps);
-    else coop_march_sdf<(RMIN ? RMIN : 1)>(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
+    coop_march_sdf<RMIN>(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
+}
+
+template <int NB>
+__global__ void __launch_bounds__(kBlock) k_scan_metaballs(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                           const __grid_constant__ WaveBuffers wb, int wave) {
+    __shared__ CoopSmem sm;
+    scan_metaballs_queue<NB>(sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
 }
 
 } // namespace
