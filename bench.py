@@ -307,9 +307,19 @@ def roofline(args, conf, device, cfg, world):
     peak_src = "measured in this run: FFMA issue-rate probe (gprt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure"
     if not fp32_peak or fp32_peak <= 0:
         fp32_peak, peak_src = 74.4, "nominal fallback: 148 SMs x 128 lanes x 2 x 1.965 GHz"
+    # DRAM traffic per launch of the same kernel from the committed ncu --set full capture (profiles/), mean over the
+    # three launches (waves) of one frame of this workload; null when no capture is committed for this config
+    traffic, traffic_src = None, None
+    try:
+        if conf["scene_id"] == 2:
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_full_k_intersect_coop.json")))
+            vals = [l["dram_bytes_total"] for l in cap["launches"] if "dram_bytes_total" in l]
+            traffic, traffic_src = round(sum(vals) / len(vals)), "profiles/r01_ncu_full_k_intersect_coop.json (dram__bytes_read.sum + dram__bytes_write.sum)"
+    except Exception:
+        pass
     roof = {"bound": "fp32", "kernel": "k_intersect_coop (all primitive types, one persistent launch per wave)",
             "achieved": round(achieved, 3), "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
-            "frac": round(achieved / fp32_peak, 4), "traffic": None, "peak_source": peak_src,
+            "frac": round(achieved / fp32_peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
             "flops_per_launch": round(flops / n_l), "launches_per_step": n_l, "avg_launch_ms": round(ms[dom] / n_l, 4),
             "share_of_step": round(ms[dom] / max(sum(ms), 1e-9), 3),
             "units_per_step": {KERNEL_NAMES[1 + t]: round(work[t]) for t in range(10) if work[t]},
