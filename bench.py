@@ -98,8 +98,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
 
-    from gpuraytracer_b200 import GPRT_MATH_FAST, GPRT_MATH_PARITY, Renderer, default_config
-    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS
+    from gpuraytracer_b200 import GPRT_MATH_FAST, GPRT_MATH_PARITY, Renderer, default_config, multigpu
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -117,138 +116,174 @@ def run_gpu(args):
     cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0  # the scene's own
     r = Renderer(scene_id=conf["scene_id"], device=local_rank, config=cfg)
     r.on_init()
+    r.create_frame_contexts()  # 3 frames in flight, like the reference's frame_count (src/Renderer.h:92)
     W, H = r.width, r.height
-    stream = torch.cuda.current_stream()
-    r.set_stream(stream.cuda_stream)
+    main = torch.cuda.current_stream()
+    n_slots = 3
+    ext = [torch.cuda.ExternalStream(r.frame_stream(j), device=dev) for j in range(n_slots)]
 
-    from gpuraytracer_b200 import multigpu
     srows = multigpu.stripe_rows_for(H, world)
     pad_rows = multigpu.max_local_rows(H, srows, world) if world > 1 else H
-    frame_local = torch.empty((pad_rows, W, 4), dtype=torch.uint8, device=dev)
-    gathered = [torch.empty_like(frame_local) for _ in range(world)] if (world > 1 and rank == 0) else None
-    frame_full = torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else frame_local
-    host_frame = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    local = [torch.empty((pad_rows, W, 4), dtype=torch.uint8, device=dev) for _ in range(n_slots)]
+    gathered = [[torch.empty_like(local[0]) for _ in range(world)] if (world > 1 and rank == 0) else None for _ in range(n_slots)]
+    full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else local[j] for j in range(n_slots)]
+    host = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(n_slots)] if rank == 0 else [None] * n_slots
+    flush = [torch.empty(192 << 20, dtype=torch.uint8, device=dev) for _ in range(n_slots)]  # each > the 126 MB L2
 
-    def frame(step, to_host):
-        """One step: update (host), dispatch, [gather + compose on rank 0], [D2H]."""
-        r.on_update(step / 60.0)
-        if world == 1:
-            if to_host:
-                r.on_render(out=host_frame.numpy())  # host in, host out through gprt_dispatch_host
+    def step(i, to_host, flush_l2):
+        """One step = one frame: update (host), [L2 flush], dispatch, [gather + compose on rank 0], [D2H].  Asynchronous:
+        frame i runs on frame slot i % 3 (own context, own stream); the *_async call first waits for that slot's previous frame."""
+        j = r.next_frame_slot()
+        r.on_update(i / 60.0)
+        with torch.cuda.stream(ext[j]):
+            if flush_l2:
+                flush[j].zero_()
+            if world == 1:
+                if to_host:
+                    r.on_render_async(host[j].data_ptr())  # host scene constants in, pinned host frame out
+                else:
+                    r.do_raytracing_async(local[j].data_ptr())
             else:
-                r.do_raytracing(frame_local.data_ptr())
-            return
-        r.do_raytracing_striped(frame_local.data_ptr(), srows, rank, world)
-        multigpu.gather_stripes(frame_local, gathered, dst=0)
-        if rank == 0:
-            multigpu.compose(frame_full, gathered, H, srows, world)
-            if to_host:
-                host_frame.copy_(frame_full, non_blocking=True)
-                stream.synchronize()
+                r.do_raytracing_striped_async(local[j].data_ptr(), srows, rank, world)
+                multigpu.gather_stripes(local[j], gathered[j], dst=0)
+                if rank == 0:
+                    multigpu.compose(full[j], gathered[j], H, srows, world)
+                    if to_host:
+                        host[j].copy_(full[j], non_blocking=True)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(steps, first_step, to_host):
-        """Sum of per-step device intervals (CUDA events on the launching stream), L2 flushed before each."""
-        total_ms, rays = 0.0, 0
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def timed(steps, first_step, to_host, flush_l2):
+        """EXACTLY `steps` steps between two barriers; device time by CUDA events that every frame stream is ordered after /
+        before (max over ranks); for the host-output path also the host wall clock, whichever is larger."""
         barrier()
-        wall0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(main)
+        for s in ext:
+            s.wait_event(e0)
         for i in range(steps):
-            flush.zero_()
-            if world > 1:
-                dist.barrier()
+            step(first_step + i, to_host, flush_l2)
+        for s in ext:
+            main.wait_stream(s)
+        e1.record(main)
+        e1.synchronize()
+        r.wait_for_gpu()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        ms = e0.elapsed_time(e1)
+        if to_host:
+            ms = max(ms, wall_ms)
+        barrier()
+        return max_over_ranks(ms)
+
+    def single_frame_latency(steps, first_step):
+        """Strictly serial: one blocking frame at a time (no frames in flight), L2 flushed before each, per-frame CUDA events."""
+        total = 0.0
+        for i in range(steps):
+            r.on_update((first_step + i) / 60.0)
+            flush[0].zero_()
+            barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0 = time.perf_counter()
-            e0.record(stream)
-            frame(first_step + i, to_host)
-            e1.record(stream)
+            e0.record(main)
+            with torch.cuda.stream(ext[0]):
+                ext[0].wait_event(e0)
+                if world == 1:
+                    r.do_raytracing(local[0].data_ptr())
+                else:
+                    r.do_raytracing_striped(local[0].data_ptr(), srows, rank, world)
+                    multigpu.gather_stripes(local[0], gathered[0], dst=0)
+                    if rank == 0:
+                        multigpu.compose(full[0], gathered[0], H, srows, world)
+            main.wait_stream(ext[0])
+            e1.record(main)
             e1.synchronize()
-            host_ms = (time.perf_counter() - t0) * 1e3
-            ms = max(e0.elapsed_time(e1), host_ms) if to_host else e0.elapsed_time(e1)
-            if world > 1:
-                t = torch.tensor([ms], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                ms = float(t.item())
-            total_ms += ms
+            total += max_over_ranks(e0.elapsed_time(e1))
+        return total / steps
+
+    def count_rays(steps, first_step):
+        """Rays traced (device counters) by exactly the frames of the timed passes (untimed, synchronous)."""
+        rays = 0
+        for i in range(steps):
+            r.on_update((first_step + i) / 60.0)
+            if world == 1:
+                r.do_raytracing(local[0].data_ptr())
+            else:
+                r.do_raytracing_striped(local[0].data_ptr(), srows, rank, world)
             c = r.counters()
             rays += int(c.radiance_rays) + int(c.shadow_rays)
-        barrier()
-        wall = time.perf_counter() - wall0
         if world > 1:
             t = torch.tensor([rays], dtype=torch.int64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             rays = int(t.item())
-        return total_ms, rays, wall
+        return rays
 
-    def pipelined(steps, first_step):
-        """K steps through Renderer.on_render_async: 3 frames in flight (the reference's frame_count), every step with
-        its host->device upload and its device->host frame copy; host wall clock around all K steps and the final wait."""
-        barrier()
-        t0 = time.perf_counter()
-        for i in range(steps):
-            r.on_update((first_step + i) / 60.0)
-            r.on_render_async(host_ring[i % len(host_ring)].data_ptr())
-        r.wait_for_gpu()
-        return (time.perf_counter() - t0) * 1e3
-
-    host_ring = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(3)] if world == 1 else []
     for i in range(args.warmup):
-        frame(i, False)
-        frame(i, True)
-    if world == 1:
-        pipelined(3 * args.warmup, 0)
+        step(i, False, True)
+    for i in range(args.warmup):
+        step(i, True, False)
+    r.wait_for_gpu()
     barrier()
     launches_per_step = r.launch_count()
+    rays = count_rays(args.steps, args.warmup)
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    dev_ms, dev_rays, dev_wall = timed(args.steps, args.warmup, False)
-    e2e_ms, e2e_rays, _ = timed(args.steps, args.warmup, True)
-    pipe_ms = pipelined(args.steps, args.warmup) if world == 1 else None
+    dev_ms = timed(args.steps, args.warmup, False, True)
+    e2e_ms = timed(args.steps, args.warmup, True, False)
+    lat_ms = single_frame_latency(min(args.steps, 10), args.warmup)
     clocks = sampler.stop() if rank == 0 else None
 
     result = None
     if rank == 0:
-        h2d, d2h = 136 + 128 * len(r.scene().per_frame), W * H * 4
-        serial = {"value": round(e2e_rays / (e2e_ms * 1e-3) / 1e6, 3), "ms_per_step": round(e2e_ms / args.steps, 4),
-                  "how": "one blocking Renderer.on_render per step (gprt_dispatch_host), CUDA events / host clock per step, L2 flushed"}
-        if pipe_ms is not None:
-            # same frames as the serial pass, so the same ray count
-            e2e = {"value": round(e2e_rays / (pipe_ms * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(pipe_ms / args.steps, 4),
-                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                   "how": "Renderer.on_render_async: 3 frames in flight on 3 streams (the reference's frame_count = 3), host scene "
-                          "constants in, pinned host RGBA8 frame out every step; host wall clock around all steps + wait_for_gpu",
-                   "serial": serial}
-        else:
-            e2e = {"value": serial["value"], "unit": UNIT, "ms_per_step": serial["ms_per_step"], "h2d_bytes_per_step": h2d,
-                   "d2h_bytes_per_step": d2h, "how": serial["how"] + "; stripes gathered to rank 0 over NCCL, then copied to the host"}
-        value = dev_rays / (dev_ms * 1e-3) / 1e6
+        value = rays / (dev_ms * 1e-3) / 1e6
+        par = "1 GPU" if world == 1 else f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, NCCL gather of the RGBA8 rows to rank 0"
         result = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": conf["workload"], "width": W, "height": H, "math_mode": args.math, "l2_flush": "256 MiB memset before every timed step",
-                       "timing": "sum of per-step CUDA-event intervals on the launching stream, max over ranks",
-                       "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, {srows}-row stripes interleaved, NCCL gather to rank 0"},
+            "config": {"workload": conf["workload"], "width": W, "height": H, "math_mode": args.math,
+                       "frames_in_flight": n_slots,
+                       "l2_flush": "192 MiB memset on the frame's stream before every timed step (and the 0.6 GB wavefront state of a frame exceeds L2)",
+                       "timing": "CUDA events ordered around all frame streams, exactly K steps between barriers, max over ranks",
+                       "parallelism": par},
             "primary_mrays_per_s": round(W * H * args.steps / (dev_ms * 1e-3) / 1e6, 3),
-            "rays_per_step": dev_rays // args.steps,
-            "e2e": e2e,
-            "gpu_launches": launches_per_step * args.steps * (3 if world == 1 else 2),
+            "rays_per_step": rays // args.steps,
+            "single_frame_ms": round(lat_ms, 4),
+            "single_frame_how": "one frame at a time (nothing in flight), L2 flushed, CUDA events per frame: the latency of a 1080p frame",
+            "e2e": {"value": round(rays / (e2e_ms * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "h2d_bytes_per_step": 136 + 128 * len(r.scene().per_frame), "d2h_bytes_per_step": W * H * 4,
+                    "how": "Renderer.on_update + on_render_async per step (public API, 3 frames in flight): host scene constants in, pinned host "
+                           "RGBA8 frame out every step; max(CUDA events, host wall clock) around all steps + wait_for_gpu"
+                           + ("" if world == 1 else "; stripes gathered to rank 0 over NCCL, composed, then copied to the host")},
+            "gpu_launches": launches_per_step * (3 * args.steps + min(args.steps, 10)),
             "clocks": clocks,
         }
-    if rank == 0:
         result["roofline"], result["roofline_hbm"], result["kernel_ms"] = roofline(args, conf, local_rank, cfg, world)
-        if world == 1:
+        if world == 1 and not args.no_cpu:
             result["cpu_baseline"] = cpu_baseline(conf, steps=2)
-    r.on_destroy()
+    # free every tensor that was used on the frame streams BEFORE the contexts (and their streams) are destroyed:
+    # the caching allocator records an event on those streams when such a block is released
+    barrier()
+    del local, gathered, full, host, flush
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    del ext
+    r.on_destroy()
     return result
 
 
@@ -395,11 +430,21 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gprt", choices=["gprt", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development runs of the large configs)")
     ap.add_argument("--math", default=os.environ.get("GPRT_BENCH_MATH", "parity"), choices=["parity", "fast"])
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "gprt":
         args.warmup = 3
-    res = run_reference(args) if args.impl == "reference" else run_gpu(args)
+    # stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        res = run_reference(args) if args.impl == "reference" else run_gpu(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if res is not None:
         print(json.dumps(res), flush=True)
 

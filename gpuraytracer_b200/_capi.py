@@ -129,6 +129,9 @@ def lib():
         "gprt_renderer_do_raytracing_stripes": (i32, [vp, u32, u32, u32, vp, vp]),
         "gprt_renderer_on_render_async": (i32, [vp, vp]),
         "gprt_renderer_do_raytracing_async": (i32, [vp, vp]),
+        "gprt_renderer_do_raytracing_stripes_async": (i32, [vp, u32, u32, u32, vp]),
+        "gprt_renderer_create_frame_contexts": (i32, [vp]),
+        "gprt_renderer_next_frame_slot": (i32, [vp]),
         "gprt_renderer_wait_for_gpu": (i32, [vp]),
         "gprt_renderer_frame_context": (vp, [vp, i32]),
         "gprt_renderer_on_size_changed": (i32, [vp, u32, u32]),
@@ -151,6 +154,7 @@ EXPORTED_SYMBOLS = [
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
     "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_render_async", "gprt_renderer_do_raytracing_async",
+    "gprt_renderer_do_raytracing_stripes_async", "gprt_renderer_create_frame_contexts", "gprt_renderer_next_frame_slot",
     "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
 ]

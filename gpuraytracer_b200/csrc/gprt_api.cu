@@ -413,6 +413,7 @@ void gprt_destroy(gprt_ctx* c) {
 
 int gprt_set_stream(gprt_ctx* c, void* cuda_stream) {
     if (!c) return GPRT_E_INVALID_ARG;
+    if ((cudaStream_t)cuda_stream == c->stream) return GPRT_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

@@ -81,6 +81,18 @@ int Renderer::do_raytracing_async(void* d_rgba8) {
                          tile, d_rgba8, (size_t)tile.w * 4, nullptr, nullptr);
 }
 
+int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
+    int rc = ensure_frame_contexts();
+    if (rc != GPRT_OK) return rc;
+    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    m_frame_index++;
+    rc = gprt_sync(c);
+    if (rc != GPRT_OK) return rc;
+    m_last_tile = {0, 0, m_scene.width, gprt_stripe_local_rows(m_scene.height, stripe_rows, rank, world)};
+    return gprt_dispatch_stripes(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
+                                 m_scene.height, stripe_rows, rank, world, d_rgba8, (size_t)m_scene.width * 4, nullptr);
+}
+
 int Renderer::wait_for_gpu() {
     int rc = GPRT_OK;
     if (m_ctx) rc = gprt_sync(m_ctx);
@@ -217,6 +229,11 @@ int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, 
 }
 int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned) { return r ? r->impl.on_render_async(h_rgba8_pinned) : GPRT_E_INVALID_ARG; }
 int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8) { return r ? r->impl.do_raytracing_async(d_rgba8) : GPRT_E_INVALID_ARG; }
+int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
+    return r ? r->impl.do_raytracing_stripes_async(stripe_rows, rank, world, d_rgba8) : GPRT_E_INVALID_ARG;
+}
+int gprt_renderer_create_frame_contexts(gprt_renderer* r) { return r ? r->impl.create_frame_contexts() : GPRT_E_INVALID_ARG; }
+int gprt_renderer_next_frame_slot(gprt_renderer* r) { return r ? r->impl.next_frame_slot() : -1; }
 int gprt_renderer_wait_for_gpu(gprt_renderer* r) { return r ? r->impl.wait_for_gpu() : GPRT_E_INVALID_ARG; }
 gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot) { return r ? r->impl.frame_context(slot) : nullptr; }
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t w, uint32_t h) {

@@ -29,6 +29,9 @@ public:
     // first waits for the slot's previous frame, like the reference waits on its frame fence.
     int on_render_async(void* h_rgba8_pinned);                   // on_render, 3 frames in flight, whole image
     int do_raytracing_async(void* d_rgba8);                      // same with device output
+    int do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8); // multi-GPU, 3 in flight
+    int create_frame_contexts() { return ensure_frame_contexts(); }
+    int next_frame_slot() const { return (int)(m_frame_index % kFrameCount); }
     int wait_for_gpu();                                          // DeviceResources::wait_for_gpu: all frames done
     gprt_ctx* frame_context(int slot);
     float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399

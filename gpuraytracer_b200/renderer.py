@@ -92,6 +92,17 @@ class Renderer:
         """do_raytracing with 3 frames in flight (device output)."""
         check(self._lib.gprt_renderer_do_raytracing_async(self._h, d_rgba8_ptr), "do_raytracing_async")
 
+    def do_raytracing_striped_async(self, d_rgba8_ptr, stripe_rows, rank, world):
+        """Multi-GPU stripes with 3 frames in flight (device output, packed local rows)."""
+        check(self._lib.gprt_renderer_do_raytracing_stripes_async(self._h, int(stripe_rows), int(rank), int(world), d_rgba8_ptr),
+              "do_raytracing_stripes_async")
+
+    def create_frame_contexts(self):
+        check(self._lib.gprt_renderer_create_frame_contexts(self._h), "create_frame_contexts")
+
+    def next_frame_slot(self) -> int:
+        return int(self._lib.gprt_renderer_next_frame_slot(self._h))
+
     def wait_for_gpu(self):
         check(self._lib.gprt_renderer_wait_for_gpu(self._h), "wait_for_gpu")
 

@@ -65,6 +65,9 @@ int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, 
  * stay valid until gprt_renderer_wait_for_gpu (or until the slot comes round again). */
 int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned);
 int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8);
+int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8);
+int gprt_renderer_create_frame_contexts(gprt_renderer* r); /* create the 3 frame contexts (and their streams) up front */
+int gprt_renderer_next_frame_slot(gprt_renderer* r);       /* slot (0..2) the next *_async call will use */
 int gprt_renderer_wait_for_gpu(gprt_renderer* r);
 gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot); /* NULL until the slot was used */
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);
