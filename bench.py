@@ -118,6 +118,7 @@ def run_gpu(args):
     r.on_init()
     r.create_frame_contexts()  # 3 frames in flight, like the reference's frame_count (src/Renderer.h:92)
     W, H = r.width, r.height
+    n_prims = len(r.scene().aabbs)
     main = torch.cuda.current_stream()
     n_slots = 3
     ext = [torch.cuda.ExternalStream(r.frame_stream(j), device=dev) for j in range(n_slots)]
@@ -262,7 +263,8 @@ def run_gpu(args):
             "single_frame_ms": round(lat_ms, 4),
             "single_frame_how": "one frame at a time (nothing in flight), L2 flushed, CUDA events per frame: the latency of a 1080p frame",
             "e2e": {"value": round(rays / (e2e_ms * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "h2d_bytes_per_step": 136 + 128 * len(r.scene().per_frame), "d2h_bytes_per_step": W * H * 4,
+                    "h2d_bytes_per_step": 136 + (0 if r.uses_device_transforms() else 128 * n_prims), "d2h_bytes_per_step": W * H * 4,
+                    "transforms": "computed on the GPU (gprt_update_transforms)" if r.uses_device_transforms() else "computed on the host, uploaded every step",
                     "how": "Renderer.on_update + on_render_async per step (public API, 3 frames in flight): host scene constants in, pinned host "
                            "RGBA8 frame out every step; max(CUDA events, host wall clock) around all steps + wait_for_gpu"
                            + ("" if world == 1 else "; stripes gathered to rank 0 over NCCL, composed, then copied to the host")},

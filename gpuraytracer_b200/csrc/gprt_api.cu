@@ -48,6 +48,9 @@ struct gprt_ctx {
     PrimRecord* d_prims = nullptr;
     float* d_per_frame = nullptr;
     uint32_t per_frame_capacity = 0;
+    uint32_t per_frame_valid = 0;      // entries of d_per_frame that hold transforms (uploaded or computed)
+    gprt_prim_anim* d_anim = nullptr;  // gprt_set_animation
+    uint32_t n_anim = 0;
     float* d_tri_pos = nullptr;
     float* d_tri_nrm = nullptr;
     float4* d_nodes = nullptr;
@@ -395,7 +398,7 @@ void gprt_destroy(gprt_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_pass_buffers(c);
-    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_per_frame); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
+    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_per_frame); cudaFree(c->d_anim); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_fb); cudaFree(c->d_fb_ids);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     for (int i = 0; i < kStagingSlots; i++) {
@@ -496,8 +499,10 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
     if (n_per_frame && !per_frame) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaSetDevice(c->device));
 
-    // every primitive's instance_index must address the uploaded transforms
-    if (c->scene.n_prims && n_per_frame <= c->max_instance_index) return GPRT_E_INVALID_ARG;
+    // every primitive's instance_index must address the transforms: uploaded now, or already on the device
+    // (gprt_update_transforms / an earlier upload) when per_frame is NULL
+    if (c->scene.n_prims && (per_frame ? n_per_frame : c->per_frame_valid) <= c->max_instance_index) return GPRT_E_INVALID_ARG;
+    if (!per_frame) n_per_frame = 0;
 
     // per-frame transforms: host -> pinned staging -> device (src/Renderer.cpp:438-443)
     if (n_per_frame) {
@@ -507,6 +512,7 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
             cudaFree(c->d_per_frame); c->d_per_frame = nullptr;
             GPRT_CUDA(c, cudaMalloc((void**)&c->d_per_frame, bytes));
             c->per_frame_capacity = n_per_frame;
+            c->per_frame_valid = 0;
         }
         if (c->staging_bytes < bytes) {
             cudaStreamSynchronize(c->stream);
@@ -520,6 +526,7 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
         std::memcpy(c->h_staging[slot], per_frame, bytes);
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_per_frame, c->h_staging[slot], bytes, cudaMemcpyHostToDevice, c->stream));
         GPRT_CUDA(c, cudaEventRecord(c->staging_done[slot], c->stream));
+        c->per_frame_valid = n_per_frame;
     }
     c->scene.per_frame = c->d_per_frame;
 
@@ -660,6 +667,44 @@ int gprt_get_kernel_profile(gprt_ctx* c, gprt_kernel_profile* out) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
             for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += wc.cand_count[t]; }
         }
+    return GPRT_OK;
+}
+
+int gprt_set_animation(gprt_ctx* c, const gprt_prim_anim* anim, uint32_t n) {
+    if (!c || (n && !anim)) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_anim); c->d_anim = nullptr; c->n_anim = 0;
+    if (!n) return GPRT_OK;
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_anim, (size_t)n * sizeof(gprt_prim_anim)));
+    GPRT_CUDA(c, cudaMemcpy(c->d_anim, anim, (size_t)n * sizeof(gprt_prim_anim), cudaMemcpyHostToDevice));
+    c->n_anim = n;
+    return GPRT_OK;
+}
+
+int gprt_update_transforms(gprt_ctx* c, float animation_time) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    if (!c->d_anim || c->n_anim != c->scene.n_prims) return GPRT_E_INVALID_ARG; // one animation record per AABB
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t n = c->n_anim;
+    if (c->per_frame_capacity < n) {
+        cudaStreamSynchronize(c->stream);
+        cudaFree(c->d_per_frame); c->d_per_frame = nullptr;
+        GPRT_CUDA(c, cudaMalloc((void**)&c->d_per_frame, (size_t)n * sizeof(gprt_prim_per_frame)));
+        c->per_frame_capacity = n;
+    }
+    update_transforms(c->d_anim, c->d_aabbs, n, animation_time, c->d_per_frame, c->stream);
+    GPRT_CUDA(c, cudaGetLastError());
+    c->per_frame_valid = n;
+    return GPRT_OK;
+}
+
+int gprt_get_transforms(gprt_ctx* c, gprt_prim_per_frame* out, uint32_t n) {
+    if (!c || !out || n > c->per_frame_valid) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    GPRT_CUDA(c, cudaMemcpyAsync(out, c->d_per_frame, (size_t)n * sizeof(gprt_prim_per_frame), cudaMemcpyDeviceToHost, c->stream));
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
     return GPRT_OK;
 }
 

@@ -21,4 +21,7 @@ int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_node
 // FP32 FMA issue-rate probe (fp32_probe.cu): best of a few launches, TFLOP/s.  Returns a cudaError_t.
 int fp32_peak_probe(void* stream, double* tflops);
 
+// transforms.cu: writes n PrimitiveInstancePerFrameBuffer entries from the static animation inputs; returns kernels launched.
+int update_transforms(const void* d_anim, const float* d_aabbs, uint32_t n, float animation_time, void* d_per_frame, void* stream);
+
 } // namespace gprt

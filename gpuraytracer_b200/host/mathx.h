@@ -2,9 +2,17 @@
 // (src/Renderer.cpp:255-265, 289-325, 742-782), restated.  DirectXMath is not vendored in the
 // reference.  Row-vector convention: v' = v * M, translation in row 3, row-major storage.
 // Everything is evaluated in double and rounded to float once when stored into the ABI structs.
+// The matrix functions are __host__ __device__ so that the per-frame transform update can run on the
+// GPU (csrc/transforms.cu) with exactly the host's arithmetic (double, no FMA contraction either side).
 #pragma once
 #include <cmath>
 #include <cstring>
+
+#if defined(__CUDACC__)
+#define GPRT_MX __host__ __device__ inline
+#else
+#define GPRT_MX inline
+#endif
 
 namespace gprt_host {
 
@@ -12,13 +20,13 @@ struct Mat4 {
     double m[4][4];
 };
 
-inline Mat4 mat_identity() {
+GPRT_MX Mat4 mat_identity() {
     Mat4 r;
-    std::memset(&r, 0, sizeof r);
-    for (int i = 0; i < 4; i++) r.m[i][i] = 1.0;
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) r.m[i][j] = (i == j) ? 1.0 : 0.0;
     return r;
 }
-inline Mat4 mat_mul(const Mat4& a, const Mat4& b) { // XMMatrixMultiply(a, b) == a * b
+GPRT_MX Mat4 mat_mul(const Mat4& a, const Mat4& b) { // XMMatrixMultiply(a, b) == a * b
     Mat4 r;
     for (int i = 0; i < 4; i++)
         for (int j = 0; j < 4; j++) {
@@ -28,12 +36,12 @@ inline Mat4 mat_mul(const Mat4& a, const Mat4& b) { // XMMatrixMultiply(a, b) ==
         }
     return r;
 }
-inline Mat4 mat_scaling(double x, double y, double z) { // XMMatrixScaling
+GPRT_MX Mat4 mat_scaling(double x, double y, double z) { // XMMatrixScaling
     Mat4 r = mat_identity();
     r.m[0][0] = x; r.m[1][1] = y; r.m[2][2] = z;
     return r;
 }
-inline Mat4 mat_translation(double x, double y, double z) { // XMMatrixTranslationFromVector
+GPRT_MX Mat4 mat_translation(double x, double y, double z) { // XMMatrixTranslationFromVector
     Mat4 r = mat_identity();
     r.m[3][0] = x; r.m[3][1] = y; r.m[3][2] = z;
     return r;
@@ -80,13 +88,13 @@ inline Mat4 mat_perspective_fov_lh(double fov_y, double aspect, double zn, doubl
     r.m[0][0] = w; r.m[1][1] = h; r.m[2][2] = q; r.m[2][3] = 1.0; r.m[3][2] = -q * zn;
     return r;
 }
-inline Mat4 mat_inverse(const Mat4& a) { // XMMatrixInverse (general 4x4, Gauss-Jordan with partial pivoting)
+GPRT_MX Mat4 mat_inverse(const Mat4& a) { // XMMatrixInverse (general 4x4, Gauss-Jordan with partial pivoting)
     double w[4][8];
     for (int i = 0; i < 4; i++)
         for (int j = 0; j < 4; j++) { w[i][j] = a.m[i][j]; w[i][j + 4] = (i == j) ? 1.0 : 0.0; }
     for (int c = 0; c < 4; c++) {
         int p = c;
-        for (int r = c + 1; r < 4; r++) if (std::fabs(w[r][c]) > std::fabs(w[p][c])) p = r;
+        for (int r = c + 1; r < 4; r++) if (fabs(w[r][c]) > fabs(w[p][c])) p = r;
         if (p != c) for (int j = 0; j < 8; j++) { double t = w[c][j]; w[c][j] = w[p][j]; w[p][j] = t; }
         const double d = w[c][c];
         for (int j = 0; j < 8; j++) w[c][j] /= d;
@@ -99,7 +107,7 @@ inline Mat4 mat_inverse(const Mat4& a) { // XMMatrixInverse (general 4x4, Gauss-
     for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = w[i][j + 4];
     return r;
 }
-inline void mat_store(const Mat4& a, float out[16]) { // XMStoreFloat4x4 (row-major)
+GPRT_MX void mat_store(const Mat4& a, float out[16]) { // XMStoreFloat4x4 (row-major)
     for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) out[i * 4 + j] = (float)a.m[i][j];
 }
 inline void mat_store_3x4(const Mat4& a, float out[3][4]) { // XMStoreFloat3x4: transposed, column-vector form

@@ -22,6 +22,27 @@ Renderer::Renderer(int scene_id, uint32_t width, uint32_t height, uint32_t grid_
         c.abi_version = GPRT_ABI_VERSION;
         m_scene.config = c;
     }
+    m_device_transforms = m_valid && m_scene.primitives.size() >= 4096;
+}
+
+SceneState& Renderer::scene() {
+    if (m_host_transforms_stale) {
+        update_aabb_primitive_attributes(m_scene, m_scene.animate_geometry_time);
+        m_host_transforms_stale = false;
+    }
+    return m_scene;
+}
+
+// What a dispatch passes as per-frame transforms: the host array, or (device mode) nothing after the GPU computed them.
+int Renderer::prepare_transforms(gprt_ctx* c, const gprt_prim_per_frame** per_frame, uint32_t* n) {
+    if (!m_device_transforms) {
+        *per_frame = m_scene.per_frame.data();
+        *n = (uint32_t)m_scene.per_frame.size();
+        return GPRT_OK;
+    }
+    *per_frame = nullptr;
+    *n = 0;
+    return gprt_update_transforms(c, m_scene.animate_geometry_time);
 }
 
 Renderer::~Renderer() { on_destroy(); }
@@ -64,8 +85,10 @@ int Renderer::on_render_async(void* h_rgba8_pinned) {
     if (rc != GPRT_OK) return rc;
     const gprt_rect tile = {0, 0, m_scene.width, m_scene.height};
     m_last_tile = tile;
-    return gprt_dispatch_host_async(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
-                                    m_scene.height, tile, h_rgba8_pinned, (size_t)tile.w * 4, nullptr);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    rc = prepare_transforms(c, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch_host_async(c, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, tile, h_rgba8_pinned, (size_t)tile.w * 4, nullptr);
 }
 
 int Renderer::do_raytracing_async(void* d_rgba8) {
@@ -77,8 +100,10 @@ int Renderer::do_raytracing_async(void* d_rgba8) {
     if (rc != GPRT_OK) return rc;
     const gprt_rect tile = {0, 0, m_scene.width, m_scene.height};
     m_last_tile = tile;
-    return gprt_dispatch(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width, m_scene.height,
-                         tile, d_rgba8, (size_t)tile.w * 4, nullptr, nullptr);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    rc = prepare_transforms(c, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch(c, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, tile, d_rgba8, (size_t)tile.w * 4, nullptr, nullptr);
 }
 
 int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
@@ -89,8 +114,11 @@ int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, u
     rc = gprt_sync(c);
     if (rc != GPRT_OK) return rc;
     m_last_tile = {0, 0, m_scene.width, gprt_stripe_local_rows(m_scene.height, stripe_rows, rank, world)};
-    return gprt_dispatch_stripes(c, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
-                                 m_scene.height, stripe_rows, rank, world, d_rgba8, (size_t)m_scene.width * 4, nullptr);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    rc = prepare_transforms(c, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch_stripes(c, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, stripe_rows, rank, world, d_rgba8,
+                                 (size_t)m_scene.width * 4, nullptr);
 }
 
 int Renderer::wait_for_gpu() {
@@ -122,6 +150,7 @@ int Renderer::create_device_dependent_resources() {
     int rc = build_geometry();
     if (rc == GPRT_OK) rc = build_shader_tables();
     if (rc == GPRT_OK) rc = build_acceleration_structures();
+    if (rc == GPRT_OK) rc = gprt_set_animation(m_ctx, m_scene.anim.data(), (uint32_t)m_scene.anim.size());
     return rc;
 }
 
@@ -142,7 +171,8 @@ int Renderer::on_update(float animate_geometry_time, float camera_orbit_deg, flo
     if (!m_valid) return GPRT_E_INVALID_ARG;
     if (camera_orbit_deg != 0.0f) rotate_camera_y(m_scene, camera_orbit_deg);
     if (light_orbit_deg != 0.0f) rotate_light_y(m_scene, light_orbit_deg);
-    update_aabb_primitive_attributes(m_scene, animate_geometry_time);
+    if (m_device_transforms) { set_animation_time(m_scene, animate_geometry_time); m_host_transforms_stale = true; }
+    else update_aabb_primitive_attributes(m_scene, animate_geometry_time);
     return GPRT_OK;
 }
 
@@ -163,23 +193,30 @@ int Renderer::do_raytracing(gprt_rect tile, void* d_rgba8, uint32_t* d_hit_ids, 
     if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
     tile = full_if_empty(tile, m_scene);
     m_last_tile = tile;
-    return gprt_dispatch(m_ctx, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
-                         m_scene.height, tile, d_rgba8, (size_t)tile.w * 4, d_hit_ids, d_rgba_f32);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    const int rc = prepare_transforms(m_ctx, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch(m_ctx, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, tile, d_rgba8, (size_t)tile.w * 4, d_hit_ids, d_rgba_f32);
 }
 
 int Renderer::do_raytracing_stripes(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8, uint32_t* d_hit_ids) {
     if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
     m_last_tile = {0, 0, m_scene.width, gprt_stripe_local_rows(m_scene.height, stripe_rows, rank, world)};
-    return gprt_dispatch_stripes(m_ctx, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
-                                 m_scene.height, stripe_rows, rank, world, d_rgba8, (size_t)m_scene.width * 4, d_hit_ids);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    const int rc = prepare_transforms(m_ctx, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch_stripes(m_ctx, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, stripe_rows, rank, world, d_rgba8,
+                                 (size_t)m_scene.width * 4, d_hit_ids);
 }
 
 int Renderer::on_render(gprt_rect tile, void* h_rgba8, uint32_t* h_hit_ids) {
     if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
     tile = full_if_empty(tile, m_scene);
     m_last_tile = tile;
-    return gprt_dispatch_host(m_ctx, &m_scene.scene_cb, m_scene.per_frame.data(), (uint32_t)m_scene.per_frame.size(), m_scene.width,
-                              m_scene.height, tile, h_rgba8, (size_t)tile.w * 4, h_hit_ids);
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    const int rc = prepare_transforms(m_ctx, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch_host(m_ctx, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, tile, h_rgba8, (size_t)tile.w * 4, h_hit_ids);
 }
 
 float Renderer::primary_mrays_per_s() {
@@ -232,6 +269,8 @@ int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8) { return 
 int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
     return r ? r->impl.do_raytracing_stripes_async(stripe_rows, rank, world, d_rgba8) : GPRT_E_INVALID_ARG;
 }
+int gprt_renderer_get_device_transforms(gprt_renderer* r) { return r && r->impl.device_transforms() ? 1 : 0; }
+int gprt_renderer_set_device_transforms(gprt_renderer* r, int on) { if (!r) return GPRT_E_INVALID_ARG; r->impl.set_device_transforms(on != 0); return GPRT_OK; }
 int gprt_renderer_create_frame_contexts(gprt_renderer* r) { return r ? r->impl.create_frame_contexts() : GPRT_E_INVALID_ARG; }
 int gprt_renderer_next_frame_slot(gprt_renderer* r) { return r ? r->impl.next_frame_slot() : -1; }
 int gprt_renderer_wait_for_gpu(gprt_renderer* r) { return r ? r->impl.wait_for_gpu() : GPRT_E_INVALID_ARG; }
@@ -241,6 +280,12 @@ int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t w, uint32_t h) {
 }
 gprt_ctx* gprt_renderer_context(gprt_renderer* r) { return r ? r->impl.context() : nullptr; }
 float gprt_renderer_primary_mrays_per_s(gprt_renderer* r) { return r ? r->impl.primary_mrays_per_s() : 0.0f; }
+
+int gprt_renderer_get_size(gprt_renderer* r, uint32_t* width, uint32_t* height) {
+    if (!r || !width || !height) return GPRT_E_INVALID_ARG;
+    *width = r->impl.size_w(); *height = r->impl.size_h();
+    return GPRT_OK;
+}
 
 int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out) {
     if (!r || !out) return GPRT_E_INVALID_ARG;

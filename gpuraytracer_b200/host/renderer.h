@@ -36,7 +36,13 @@ public:
     gprt_ctx* frame_context(int slot);
     float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399
 
-    SceneState& scene() { return m_scene; }
+    // Per-frame transforms on the GPU (gprt_update_transforms) instead of host arithmetic + upload; on by default for
+    // scenes of >= 4096 primitives.  The host copy is then refreshed only when scene() is asked for it.
+    void set_device_transforms(bool on) { m_device_transforms = on; }
+    bool device_transforms() const { return m_device_transforms; }
+    SceneState& scene();
+    uint32_t size_w() const { return m_scene.width; }
+    uint32_t size_h() const { return m_scene.height; }
     gprt_ctx* context() { return m_ctx; }
     bool valid() const { return m_valid; }
 
@@ -53,6 +59,9 @@ private:
     gprt_ctx* m_frame_ctx[kFrameCount] = {nullptr, nullptr, nullptr};
     uint32_t m_frame_index = 0;
     int m_device = -1;
+    int prepare_transforms(gprt_ctx* c, const gprt_prim_per_frame** per_frame, uint32_t* n);
+    bool m_device_transforms = false;
+    bool m_host_transforms_stale = false;
     bool m_valid = false;
     bool m_initialized = false;
     gprt_rect m_last_tile = {0, 0, 0, 0};

@@ -160,6 +160,11 @@ void rotate_light_y(SceneState& s, float degrees) { // src/Renderer.cpp:104-110
     for (int i = 0; i < 4; i++) s.scene_cb.light_position[i] = (float)o[i];
 }
 
+void set_animation_time(SceneState& s, float animation_time) {
+    s.animate_geometry_time = animation_time;
+    s.scene_cb.elapsed_time = animation_time; // src/Renderer.cpp:119
+}
+
 void update_aabb_primitive_attributes(SceneState& s, float animation_time) { // src/Renderer.cpp:302-356
     s.animate_geometry_time = animation_time;
     s.scene_cb.elapsed_time = animation_time; // src/Renderer.cpp:119
@@ -188,7 +193,12 @@ void build_geometry_and_tables(SceneState& s) {
     }
     // AABBs
     s.aabbs.resize(s.primitives.size());
-    for (size_t i = 0; i < s.primitives.size(); i++) s.aabbs[i] = s.primitives[i].aabb;
+    s.anim.resize(s.primitives.size());
+    for (size_t i = 0; i < s.primitives.size(); i++) {
+        s.aabbs[i] = s.primitives[i].aabb;
+        for (int k = 0; k < 3; k++) s.anim[i].scale[k] = s.primitives[i].scale[k];
+        s.anim[i].rotates = s.primitives[i].rotates ? 1u : 0u;
+    }
 
     // build_bottom_level_as_instance_descs, src/Renderer.cpp:732-786
     std::memset(s.instances, 0, sizeof s.instances);

@@ -42,6 +42,7 @@ struct SceneState {
     gprt_scene_cb scene_cb;
     std::vector<gprt_prim_per_frame> per_frame;
     std::vector<gprt_aabb> aabbs;
+    std::vector<gprt_prim_anim> anim;   // static inputs of update_aabb_primitive_attributes (for the on-device update)
     std::vector<gprt_hit_group_record> hit_groups;
     std::vector<gprt_vertex> vertices;
     std::vector<uint16_t> indices;
@@ -61,6 +62,7 @@ bool build_scene(SceneState& s, int scene_id, uint32_t width, uint32_t height, u
 void initialize_camera(SceneState& s, const double eye[3], const double at[3]); // initialize_scene, camera part
 void update_camera_matrices(SceneState& s);                                     // src/Renderer.cpp:289-300
 void update_aabb_primitive_attributes(SceneState& s, float animation_time);     // src/Renderer.cpp:302-356
+void set_animation_time(SceneState& s, float animation_time);                   // the same without the per-primitive matrices
 void rotate_camera_y(SceneState& s, float degrees);                             // on_update camera orbit, :92-101
 void rotate_light_y(SceneState& s, float degrees);                              // on_update light orbit, :104-110
 void build_geometry_and_tables(SceneState& s);                                  // build_geometry + instance descs + shader tables

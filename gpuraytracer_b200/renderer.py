@@ -97,6 +97,20 @@ class Renderer:
         check(self._lib.gprt_renderer_do_raytracing_stripes_async(self._h, int(stripe_rows), int(rank), int(world), d_rgba8_ptr),
               "do_raytracing_stripes_async")
 
+    def set_device_transforms(self, on: bool):
+        """Per-frame transforms computed on the GPU (default for scenes of >= 4096 primitives) or on the host."""
+        check(self._lib.gprt_renderer_set_device_transforms(self._h, 1 if on else 0), "set_device_transforms")
+
+    def uses_device_transforms(self) -> bool:
+        return bool(self._lib.gprt_renderer_get_device_transforms(self._h))
+
+    def device_transforms(self) -> np.ndarray:
+        """The transforms currently resident on the device of frame slot 0 (tests)."""
+        n = len(self.scene().aabbs)
+        out = np.zeros(n, dtype=_capi.PER_FRAME_DTYPE)
+        check(self._lib.gprt_get_transforms(self.context, out.ctypes.data, n), "get_transforms")
+        return out
+
     def create_frame_contexts(self):
         check(self._lib.gprt_renderer_create_frame_contexts(self._h), "create_frame_contexts")
 
@@ -157,13 +171,18 @@ class Renderer:
         check(self._lib.gprt_renderer_scene(self._h, C.byref(v)), "scene")
         return v
 
+    def _size(self):
+        w, h = C.c_uint32(0), C.c_uint32(0)
+        check(self._lib.gprt_renderer_get_size(self._h, C.byref(w), C.byref(h)), "get_size")
+        return int(w.value), int(h.value)
+
     @property
     def width(self):
-        return self._view().width
+        return self._size()[0]
 
     @property
     def height(self):
-        return self._view().height
+        return self._size()[1]
 
     def scene(self) -> SceneData:
         v = self._view()

@@ -245,6 +245,23 @@ int gprt_dispatch_host(gprt_ctx* ctx, const gprt_scene_cb* scene,
                        uint32_t width, uint32_t height, gprt_rect tile,
                        void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids);
 
+/* Static inputs of Renderer::update_aabb_primitive_attributes (src/Renderer.cpp:302-356) for primitive i
+ * (i == its instance_index): transform(t) = scaling(scale) * (rotates ? rotationY(-2 t) : I) *
+ * translation(centre of AABB i).  16 bytes. */
+typedef struct gprt_prim_anim {
+    float    scale[3];
+    uint32_t rotates;
+} gprt_prim_anim;
+
+/* Keep the per-frame transforms on the device: upload the animation inputs once ... */
+int gprt_set_animation(gprt_ctx* ctx, const gprt_prim_anim* anim, uint32_t n);
+/* ... then, per frame, compute all n PrimitiveInstancePerFrameBuffer entries on the GPU (same arithmetic
+ * as the host path, bit-identical matrices) instead of uploading 128 bytes per primitive.  A following
+ * gprt_dispatch* call with per_frame == NULL uses them.  Asynchronous on the context stream. */
+int gprt_update_transforms(gprt_ctx* ctx, float animation_time);
+/* Read the device-resident transforms back (tests). */
+int gprt_get_transforms(gprt_ctx* ctx, gprt_prim_per_frame* out, uint32_t n);
+
 /* Multi-GPU sharding (no counterpart in the single-GPU reference): the frame is cut into stripes of
  * `stripe_rows` rows dealt round-robin to `world` ranks; rank r renders stripes r, r + world, ...
  * into a PACKED buffer of gprt_stripe_local_rows() rows (local row l at d_rgba8 + l * pitch_bytes,

@@ -66,13 +66,18 @@ int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, 
 int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned);
 int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8);
 int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8);
+/* Compute the per-frame transforms on the GPU (gprt_update_transforms) instead of on the host + 128 B/primitive upload.
+ * Default: on for scenes of >= 4096 primitives. */
+int gprt_renderer_set_device_transforms(gprt_renderer* r, int on);
+int gprt_renderer_get_device_transforms(gprt_renderer* r);
 int gprt_renderer_create_frame_contexts(gprt_renderer* r); /* create the 3 frame contexts (and their streams) up front */
 int gprt_renderer_next_frame_slot(gprt_renderer* r);       /* slot (0..2) the next *_async call will use */
 int gprt_renderer_wait_for_gpu(gprt_renderer* r);
 gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot); /* NULL until the slot was used */
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);
 
-int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out);
+int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out); /* refreshes the host transforms if they are computed on the device */
+int gprt_renderer_get_size(gprt_renderer* r, uint32_t* width, uint32_t* height);
 gprt_ctx* gprt_renderer_context(gprt_renderer* r);
 
 /* Frame statistics in the reference's convention (calculate_frame_stats,

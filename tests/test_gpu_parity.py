@@ -205,6 +205,34 @@ def test_frames_in_flight_equal_synchronous_frames():
             np.testing.assert_array_equal(a, d.cpu().numpy())
 
 
+def test_device_side_transform_update_is_bit_identical():
+    """gprt_update_transforms (update_aabb_primitive_attributes on the GPU) writes exactly the matrices the
+    host path computes, so images do not change; it is the default from 4096 primitives up."""
+    for t in (0.0, 0.37, 2.5):
+        with Renderer(scene_id=5, width=320, height=180, grid_n=64, device=0, config=make_cfg()) as r:  # 4096 primitives
+            r.on_init()
+            r.on_update(t)
+            a, _ = r.on_render()
+            a = a.copy()
+            dev = r.device_transforms()
+            host = r.scene().per_frame
+            assert dev.tobytes() == host.tobytes()
+            r.set_device_transforms(False)
+            r.on_update(t)
+            b, _ = r.on_render()
+            np.testing.assert_array_equal(a, b)
+    with Renderer(scene_id=0, width=320, height=180, device=0, config=make_cfg()) as r:  # rotating primitives, both modes
+        r.on_init()
+        r.on_update(1.3)
+        a, _ = r.on_render()
+        a = a.copy()
+        r.set_device_transforms(True)
+        r.on_update(1.3)
+        b, _ = r.on_render()
+        np.testing.assert_array_equal(a, b)
+        assert r.device_transforms().tobytes() == r.scene().per_frame.tobytes()
+
+
 def test_internal_banding_is_invisible():
     """A frame larger than the internal pass size is rendered in bands; compare against tiles."""
     with Renderer(scene_id=0, width=2560, height=1800, device=0, config=make_cfg()) as r:  # 4.6 Mpx > 2^22
