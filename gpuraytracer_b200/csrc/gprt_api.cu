@@ -46,6 +46,7 @@ struct gprt_ctx {
     // device scene
     float* d_aabbs = nullptr;
     PrimRecord* d_prims = nullptr;
+    uint8_t* d_prim_types = nullptr;   // type id per primitive, tagged into the LBVH leaf refs
     float* d_per_frame = nullptr;
     uint32_t per_frame_capacity = 0;
     uint32_t per_frame_valid = 0;      // entries of d_per_frame that hold transforms (uploaded or computed)
@@ -224,11 +225,14 @@ int upload_static_scene(gprt_ctx* c) {
     if (n_tris && c->tri_contrib >= c->h_records.size()) return GPRT_E_INVALID_ARG;
 
     cudaStreamSynchronize(c->stream);
-    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
+    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch);
-    c->d_aabbs = nullptr; c->d_prims = nullptr; c->d_tri_pos = c->d_tri_nrm = nullptr; c->d_nodes = nullptr; c->d_sorted = nullptr; c->d_lbvh_scratch = nullptr;
+    c->d_aabbs = nullptr; c->d_prims = nullptr; c->d_prim_types = nullptr; c->d_tri_pos = c->d_tri_nrm = nullptr; c->d_nodes = nullptr; c->d_sorted = nullptr; c->d_lbvh_scratch = nullptr;
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_aabbs, (size_t)(n ? n : 1) * 6 * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_prims, (size_t)(n ? n : 1) * sizeof(PrimRecord)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_prim_types, (size_t)(n ? n : 1)));
+    std::vector<uint8_t> types(n);
+    for (uint32_t i = 0; i < n; i++) types[i] = (uint8_t)prims[i].type_id;
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_pos, (tri_pos.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_nrm, (tri_nrm.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_nodes, (size_t)(n ? n : 1) * 4 * sizeof(float4)));
@@ -237,6 +241,7 @@ int upload_static_scene(gprt_ctx* c) {
     if (n) {
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_prims, prims.data(), (size_t)n * sizeof(PrimRecord), cudaMemcpyHostToDevice, c->stream));
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_prim_types, types.data(), (size_t)n, cudaMemcpyHostToDevice, c->stream));
     }
     if (n_tris) {
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_pos, tri_pos.data(), tri_pos.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
@@ -398,7 +403,7 @@ void gprt_destroy(gprt_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_pass_buffers(c);
-    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_per_frame); cudaFree(c->d_anim); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
+    cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_per_frame); cudaFree(c->d_anim); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_fb); cudaFree(c->d_fb_ids);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     for (int i = 0; i < kStagingSlots; i++) {
@@ -429,7 +434,7 @@ int gprt_set_geometry(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs, con
                       const uint16_t* indices, uint32_t n_indices, const gprt_instance_desc* instances, uint32_t n_instances) {
     if (!c || (n_aabbs && !aabbs) || (n_vertices && !vertices) || (n_indices && !indices) || (n_instances && !instances)) return GPRT_E_INVALID_ARG;
     if (n_indices % 3 != 0) return GPRT_E_INVALID_ARG;
-    if (n_aabbs >= (1u << 28)) return GPRT_E_UNSUPPORTED;
+    if (n_aabbs >= (1u << 27)) return GPRT_E_UNSUPPORTED; // leaf refs: 27 bits of primitive index + 4 bits of type
     if (n_instances > 2) return GPRT_E_UNSUPPORTED; // the reference's TLAS: one triangle BLAS instance + one AABB BLAS instance
     c->have_tri_instance = c->have_aabb_instance = false;
     for (uint32_t i = 0; i < n_instances; i++) {
@@ -467,7 +472,7 @@ int gprt_build_accel(gprt_ctx* c) {
     if (rc != GPRT_OK) return rc;
     GPRT_CUDA(c, cudaEventRecord(c->ev_build0, c->stream));
     int32_t root = INT32_MIN;
-    lbvh_build(c->d_aabbs, c->scene.n_prims, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, &root, c->stream);
+    lbvh_build(c->d_aabbs, c->scene.n_prims, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, &root, c->stream, c->d_prim_types);
     GPRT_CUDA(c, cudaEventRecord(c->ev_build1, c->stream));
     GPRT_CUDA(c, cudaGetLastError());
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream)); // blocking, like wait_for_gpu at src/Renderer.cpp:827
@@ -484,7 +489,7 @@ int gprt_refit_accel(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs) {
     GPRT_CUDA(c, cudaSetDevice(c->device));
     c->h_aabbs.assign(aabbs, aabbs + n_aabbs);
     GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n_aabbs * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
-    lbvh_refit(c->d_aabbs, n_aabbs, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, c->stream);
+    lbvh_refit(c->d_aabbs, n_aabbs, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, c->stream, c->d_prim_types);
     GPRT_CUDA(c, cudaGetLastError());
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
     return GPRT_OK;

@@ -209,7 +209,7 @@ __device__ __forceinline__ void load_child_box(int32_t ref, const float* aabbs, 
 
 __global__ void k_refit(const float* __restrict__ aabbs, const uint32_t* __restrict__ sorted_prims, int n, const int32_t* __restrict__ children,
                         const int32_t* __restrict__ parent_internal, const int32_t* __restrict__ parent_leaf, uint32_t* flags, float* node_boxes,
-                        float4* nodes) {
+                        float4* nodes, const uint8_t* __restrict__ prim_tags) {
     const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
     if (leaf >= n) return;
     int node = parent_leaf[leaf];
@@ -228,8 +228,10 @@ __global__ void k_refit(const float* __restrict__ aabbs, const uint32_t* __restr
             nb[k + 3] = fmaxf(hi0[k], hi1[k]);
         }
         // leaf refs in the final nodes name the ORIGINAL primitive index
-        const int32_t f0 = r0 < 0 ? ~(int32_t)sorted_prims[~r0] : r0;
-        const int32_t f1 = r1 < 0 ? ~(int32_t)sorted_prims[~r1] : r1;
+        // (and, in bits 27..30, the caller's per-primitive tag: the traversal reads the primitive type from the ref)
+        int32_t f0 = r0, f1 = r1;
+        if (r0 < 0) { const uint32_t p = sorted_prims[~r0]; f0 = ~(int32_t)(p | (prim_tags ? (uint32_t)prim_tags[p] << 27 : 0u)); }
+        if (r1 < 0) { const uint32_t p = sorted_prims[~r1]; f1 = ~(int32_t)(p | (prim_tags ? (uint32_t)prim_tags[p] << 27 : 0u)); }
         float4* out = nodes + 4 * (size_t)node;
         out[0] = make_float4(lo0[0], lo0[1], lo0[2], hi0[0]);
         out[1] = make_float4(hi0[1], hi0[2], lo1[0], lo1[1]);
@@ -254,7 +256,8 @@ size_t lbvh_scratch_bytes(uint32_t n) {
     return b + 16 * 256; // every sub-allocation is rounded up to 256 bytes
 }
 
-int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* stream_) {
+int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* stream_,
+               const uint8_t* d_prim_tags) {
     cudaStream_t s = (cudaStream_t)stream_;
     int launches = 0;
     if (n == 0) { *root_ref = INT32_MIN; return 0; }
@@ -294,12 +297,13 @@ int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_node
     cudaMemcpyAsync(d_sorted_prims, vi, (size_t)n * 4, cudaMemcpyDeviceToDevice, s);
     k_karras<<<grid_n, kBlock, 0, s>>>(ki, (int)n, children, parent_internal, parent_leaf); launches++;
     cudaMemsetAsync(flags, 0, (size_t)n * 4, s);
-    k_refit<<<grid_n, kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes); launches++;
+    k_refit<<<grid_n, kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes, d_prim_tags); launches++;
     *root_ref = 0;
     return launches;
 }
 
-int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream_) {
+int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream_,
+               const uint8_t* d_prim_tags) {
     // scratch layout must match lbvh_build (children / parents are reused)
     cudaStream_t s = (cudaStream_t)stream_;
     if (n < 2) return 0;
@@ -315,7 +319,7 @@ int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_node
     uint32_t* flags = (uint32_t*)take((size_t)n * 4);
     float* node_boxes = (float*)take(6 * (size_t)n * 4);
     cudaMemsetAsync(flags, 0, (size_t)n * 4, s);
-    k_refit<<<(int)((n + kBlock - 1) / kBlock), kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes);
+    k_refit<<<(int)((n + kBlock - 1) / kBlock), kBlock, 0, s>>>(d_aabbs, d_sorted_prims, (int)n, children, parent_internal, parent_leaf, flags, node_boxes, d_nodes, d_prim_tags);
     return 1;
 }
 

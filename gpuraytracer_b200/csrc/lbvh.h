@@ -13,10 +13,12 @@ size_t lbvh_scratch_bytes(uint32_t n);
 // Builds the tree over d_aabbs (6 floats per primitive).  d_nodes: 4 float4 per internal node
 // (n - 1 nodes).  d_sorted_prims: n uint32 (primitive index per Morton-sorted leaf).
 // root_ref: 0 (internal root), ~0 (single leaf) or INT32_MIN (empty).  Returns kernels launched.
-int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* stream);
+int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* stream,
+               const uint8_t* d_prim_tags = nullptr); // optional 4-bit tag per primitive, stored in bits 27..30 of its leaf ref
 
 // Recomputes the node boxes bottom-up for moved AABBs, topology unchanged.
-int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream);
+int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream,
+               const uint8_t* d_prim_tags = nullptr);
 
 // FP32 FMA issue-rate probe (fp32_probe.cu): best of a few launches, TFLOP/s.  Returns a cudaError_t.
 int fp32_peak_probe(void* stream, double* tflops);
