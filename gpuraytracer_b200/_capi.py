@@ -47,7 +47,8 @@ class KernelProfile(C.Structure):
 
 class WaveStats(C.Structure):
     _fields_ = [("n_radiance", C.c_uint32), ("n_shadow", C.c_uint32), ("candidates", C.c_uint32 * 10), ("work", C.c_uint32 * 10),
-                ("max_evals", C.c_uint32 * 10), ("evals_hist", (C.c_uint32 * 12) * 10)]
+                ("max_evals", C.c_uint32 * 10), ("evals_hist", (C.c_uint32 * 12) * 10),
+                ("node_visits", C.c_uint32), ("max_node_visits", C.c_uint32)]
 
 
 class Timing(C.Structure):

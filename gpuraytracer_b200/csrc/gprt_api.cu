@@ -20,6 +20,8 @@ namespace {
 constexpr uint32_t kDefaultPassPixels = 1u << 22; // pixels per internal pass (bounds queue memory)
 constexpr int kStagingSlots = 3;                  // == frame_count of the reference (src/Renderer.h:92)
 constexpr int kMaxBands = 256;
+constexpr uint32_t kSpillBudget = 64;     // LBVH node fetches one thread spends on a ray before handing the rest of the walk on
+constexpr uint32_t kSpillMinPrims = 4096; // below this no ray walks long enough to matter and the spill rounds are not launched
 
 struct HostCtrlCopy { WaveCtrl ctrl[kMaxDepth + 2]; };
 
@@ -46,6 +48,7 @@ struct gprt_ctx {
     // device scene
     float* d_aabbs = nullptr;
     PrimRecord* d_prims = nullptr;
+    uint32_t spill_budget = 0;         // LBVH node fetches per thread before a walk is handed to the next spill round
     uint8_t* d_prim_types = nullptr;   // type id per primitive, tagged into the LBVH leaf refs
     float* d_per_frame = nullptr;
     uint32_t per_frame_capacity = 0;
@@ -175,6 +178,8 @@ int ensure_pass_buffers(gprt_ctx* c, uint32_t pixels) {
         A(c->wb.cand_res[t], cap);
     }
     A(c->wb.ctrl, (size_t)(kMaxDepth + 2));
+    A(c->wb.spill[0], P); A(c->wb.spill[1], P);
+    c->wb.spill_capacity = (uint32_t)P;
     A(c->wb.lvl_o_t, P * depth);
     A(c->wb.lvl_d, P * depth);
     A(c->wb.lvl_n, P * depth);
@@ -313,6 +318,7 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     pp.ray_capacity = 2 * pp.n_pixels;
     pp.cand_capacity = c->cand_capacity;
     pp.brute_force = (c->cfg.flags & GPRT_FLAG_BRUTE_FORCE_TRAVERSAL) ? 1u : 0u;
+    pp.spill_budget = (!pp.brute_force && c->scene.n_prims >= kSpillMinPrims) ? c->spill_budget : 0u;
     pp.stripe_rows = st.rows; pp.stripe_rank = st.rank; pp.stripe_world = st.world;
 
     const uint32_t D = pp.max_depth;
@@ -382,6 +388,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     c->kt = kernels_parity();
     c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : kernels_parity();
     { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
+    { const char* e = getenv("GPRT_SPILL_BUDGET"); c->spill_budget = e ? (uint32_t)atoi(e) : kSpillBudget; } // tuning aid
     std::memset(&c->scene, 0, sizeof c->scene);
     std::memset(&c->wb, 0, sizeof c->wb);
     std::memset(c->h_instances, 0, sizeof c->h_instances);
@@ -721,6 +728,8 @@ int gprt_get_wave_stats(gprt_ctx* c, uint32_t wave, gprt_wave_stats* out) {
     const WaveCtrl& wc = c->h_ctrl[0].ctrl[wave];
     out->n_radiance = wc.n_radiance;
     out->n_shadow = wc.n_shadow;
+    out->node_visits = wc.node_visits;
+    out->max_node_visits = wc.max_node_visits;
     for (int t = 0; t < kNumTypes; t++) {
         out->candidates[t] = wc.cand_count[t];
         out->work[t] = wc.work[t];

@@ -77,10 +77,67 @@ __device__ __forceinline__ void add_candidate(const PassParams& pp, const WaveBu
     }
 }
 
+// Walks the subtree under `root` for ray r; every box whose slab test passes on [TMin, tcur] is a candidate.
+// A grazing ray crosses hundreds of boxes (2000+ dependent node fetches at 1 M primitives), and left to one thread
+// that chain, not the throughput, sets the kernel's duration.  So a walk has a node budget (pp.spill_budget), after
+// which the unwalked rest goes to the next spill round as (ray, subtree) entries:
+//   kWalkDepthFirst       no budget (small scenes, last round)
+//   kWalkDepthFirstBudget the main kernel: cheap for the common short ray; the handed-over stack is lopsided (its
+//                         bottom entries are the big far subtrees)
+//   kWalkBreadthFirst     the spill rounds: expanding the oldest entry first opens the top levels of a big subtree,
+//                         so what is handed on are ~budget pieces of similar size and the chain shrinks by that
+//                         factor per round instead of halving
+// The candidate set does not depend on the visiting order.  Returns the nodes fetched.
+enum WalkMode { kWalkDepthFirst = 0, kWalkDepthFirstBudget = 1, kWalkBreadthFirst = 2 };
+constexpr uint32_t kBreadthBudgetMax = 48; // the frontier grows by at most one entry per fetch and must fit the 64-entry ring
+
+template <int MODE>
+__device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, V3 oo, V3 inv_d,
+                                              float tcur, int32_t root, uint2* spill_q, uint32_t* spill_count, Pending& pend) {
+    const float tmin = 0.0f;
+    int32_t ring[64];
+    uint32_t head = 0, tail = 0; // live entries: ring[head .. tail) mod 64
+    ring[tail++] = root;
+    uint32_t visits = 0;
+    uint32_t budget = 0xFFFFFFFFu;
+    if (MODE == kWalkDepthFirstBudget && pp.spill_budget) budget = pp.spill_budget;
+    if (MODE == kWalkBreadthFirst) budget = min(max(pp.spill_budget, 1u), kBreadthBudgetMax);
+    while (tail != head) {
+        if (MODE != kWalkDepthFirst && visits >= budget) {
+            const uint32_t n = tail - head;
+            const uint32_t at = atomicAdd(spill_count, n);
+            if (at + n <= wb.spill_capacity) {
+                for (uint32_t i = 0; i < n; i++) spill_q[at + i] = make_uint2(r, (uint32_t)ring[(head + i) & 63u]);
+                break;
+            }
+            // queue full: void the reserved slots that exist and finish the walk here
+            for (uint32_t i = 0; i < n && at + i < wb.spill_capacity; i++) spill_q[at + i] = make_uint2(0xFFFFFFFFu, 0u);
+            budget = 0xFFFFFFFFu;
+        }
+        const bool oldest_first = MODE == kWalkBreadthFirst && budget != 0xFFFFFFFFu;
+        const int32_t node = oldest_first ? ring[head++ & 63u] : ring[--tail & 63u];
+        visits++;
+        const float4* n4 = sc.bvh_nodes + 4 * (size_t)node;
+        const float4 a = __ldg(n4), b = __ldg(n4 + 1), c = __ldg(n4 + 2), e = __ldg(n4 + 3);
+        const float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {a.w, b.x, b.y};
+        const float lo1[3] = {b.z, b.w, c.x}, hi1[3] = {c.y, c.z, c.w};
+        const int32_t ref0 = __float_as_int(e.x), ref1 = __float_as_int(e.y);
+        if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
+            if (ref0 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref0 & kLeafPrimMask, (uint32_t)~ref0 >> kLeafTypeShift, pend);
+            else if (tail - head < 64u) ring[tail++ & 63u] = ref0;
+        }
+        if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
+            if (ref1 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref1 & kLeafPrimMask, (uint32_t)~ref1 >> kLeafTypeShift, pend);
+            else if (tail - head < 64u) ring[tail++ & 63u] = ref1;
+        }
+    }
+    return visits;
+}
+
 // One ray: plane, then the AABB tree.  Writes hitkey / ray_tcur, collects candidates in `pend`.
 template <bool PRIMARY>
-__device__ __forceinline__ void traverse_ray(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, uint32_t r,
-                                             Pending& pend) {
+__device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, uint32_t r,
+                                                 Pending& pend) {
     V3 o, d;
     uint32_t meta;
     if (PRIMARY) {
@@ -126,10 +183,10 @@ __device__ __forceinline__ void traverse_ray(const SceneDev& sc, const PassParam
     }
     wb.hitkey[r] = key;
     wb.ray_tcur[r] = tcur;
-    if (shadow && key != kKeyMiss) return; // ACCEPT_FIRST_HIT_AND_END_SEARCH
-    if (!sc.has_aabb_instance || sc.n_prims == 0) return;
+    if (shadow && key != kKeyMiss) return 0u; // ACCEPT_FIRST_HIT_AND_END_SEARCH
+    if (!sc.has_aabb_instance || sc.n_prims == 0) return 0u;
 
-    // (ii) procedural AABBs: every box whose slab test passes on [TMin, tcur] is a candidate
+    // (ii) procedural AABBs
     const V3 oo = xform_point_3x4(sc.aabb_w2o, o), dd = xform_vector_3x4(sc.aabb_w2o, d);
     const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
     if (pp.brute_force || sc.root_ref < 0) {
@@ -137,68 +194,125 @@ __device__ __forceinline__ void traverse_ray(const SceneDev& sc, const PassParam
             const float* b = sc.aabbs + 6 * i;
             if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) add_candidate(pp, wb, ctrl, r, i, sc.prims[i].type_id, pend);
         }
-    } else {
-        int32_t stack[64];
-        int sp = 0;
-        stack[sp++] = sc.root_ref;
-        while (sp) {
-            const int32_t node = stack[--sp];
-            const float4* n4 = sc.bvh_nodes + 4 * (size_t)node;
-            const float4 a = __ldg(n4), b = __ldg(n4 + 1), c = __ldg(n4 + 2), e = __ldg(n4 + 3);
-            const float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {a.w, b.x, b.y};
-            const float lo1[3] = {b.z, b.w, c.x}, hi1[3] = {c.y, c.z, c.w};
-            const int32_t ref0 = __float_as_int(e.x), ref1 = __float_as_int(e.y);
-            if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
-                if (ref0 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref0 & kLeafPrimMask, (uint32_t)~ref0 >> kLeafTypeShift, pend);
-                else if (sp < 64) stack[sp++] = ref0;
-            }
-            if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
-                if (ref1 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref1 & kLeafPrimMask, (uint32_t)~ref1 >> kLeafTypeShift, pend);
-                else if (sp < 64) stack[sp++] = ref1;
-            }
-        }
+        return 0u;
     }
+    return walk_tree<kWalkDepthFirstBudget>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, sc.root_ref, wb.spill[0], &ctrl->spill_count[0], pend);
 }
 
+// Convergent append of a warp's pending candidates (all 32 lanes call this).
+__device__ __forceinline__ void flush_pending(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, const Pending& pend,
+                                              uint32_t (*s_cnt)[kNumTypes], uint32_t (*s_base)[kNumTypes]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (!__any_sync(kFull, pend.n > 0)) return;
+    if (lane < kNumTypes) s_cnt[warp][lane] = 0u;
+    __syncwarp();
+    uint32_t rank[kMaxPending];
+#pragma unroll
+    for (int k = 0; k < kMaxPending; k++)
+        rank[k] = (k < pend.n) ? atomicAdd(&s_cnt[warp][pend.e[k] >> kLeafTypeShift], 1u) : 0u;
+    __syncwarp();
+    if (lane < kNumTypes) {
+        const uint32_t c = s_cnt[warp][lane];
+        s_base[warp][lane] = c ? atomicAdd(&ctrl->cand_count[lane], c) : 0u;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kMaxPending; k++)
+        if (k < pend.n) {
+            const uint32_t type = pend.e[k] >> kLeafTypeShift;
+            const uint32_t idx = s_base[warp][type] + rank[k];
+            if (idx < pp.cand_capacity) wb.cand[type][idx] = make_uint2(r, pend.e[k] & kLeafPrimMask);
+            else ctrl->overflow = 1u;
+        }
+    __syncwarp();
+}
+
+// traversal statistics (gprt_get_wave_stats): kept per lane, two atomics per warp when the kernel ends
+// (same-address atomics retire at about one per two clocks: per batch of 32 rays they cost 0.2 ms at 1080p)
+struct VisitStats {
+    uint32_t sum = 0, most = 0;
+    __device__ __forceinline__ void add(uint32_t visits) { sum += visits; most = max(most, visits); }
+    __device__ __forceinline__ void commit(WaveCtrl* ctrl) const {
+        const uint32_t vsum = __reduce_add_sync(kFull, sum), vmax = __reduce_max_sync(kFull, most);
+        if ((threadIdx.x & 31) == 0 && vsum) { atomicAdd(&ctrl->node_visits, vsum); atomicMax(&ctrl->max_node_visits, vmax); }
+    }
+};
+
 template <bool PRIMARY>
-__global__ void __launch_bounds__(kBlock) k_traverse(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                     const __grid_constant__ WaveBuffers wb, int wave) {
+__global__ void __launch_bounds__(kBlock, 6) k_traverse(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                        const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     const uint32_t n_rays = PRIMARY ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
-    const uint32_t n_round = (n_rays + 31u) & ~31u; // whole warps stay in the loop together
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_round; r += gridDim.x * blockDim.x) {
+    VisitStats stats;
+    auto walk_batch = [&](uint32_t base) {
+        const uint32_t r = base + (uint32_t)lane;
         Pending pend;
         pend.n = 0;
 #pragma unroll
         for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
-        if (r < n_rays) traverse_ray<PRIMARY>(sc, pp, wb, ctrl, pq, r, pend);
-        // ---- convergent append of the warp's pending candidates ----
-        if (!__any_sync(kFull, pend.n > 0)) continue;
-        if (lane < kNumTypes) s_cnt[warp][lane] = 0u;
-        __syncwarp();
-        uint32_t rank[kMaxPending];
-#pragma unroll
-        for (int k = 0; k < kMaxPending; k++)
-            rank[k] = (k < pend.n) ? atomicAdd(&s_cnt[warp][pend.e[k] >> kLeafTypeShift], 1u) : 0u;
-        __syncwarp();
-        if (lane < kNumTypes) {
-            const uint32_t c = s_cnt[warp][lane];
-            s_base[warp][lane] = c ? atomicAdd(&ctrl->cand_count[lane], c) : 0u;
-        }
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < kMaxPending; k++)
-            if (k < pend.n) {
-                const uint32_t type = pend.e[k] >> kLeafTypeShift;
-                const uint32_t idx = s_base[warp][type] + rank[k];
-                if (idx < pp.cand_capacity) wb.cand[type][idx] = make_uint2(r, pend.e[k] & kLeafPrimMask);
-                else ctrl->overflow = 1u;
-            }
-        __syncwarp();
+        uint32_t visits = 0;
+        if (r < n_rays) visits = traverse_ray<PRIMARY>(sc, pp, wb, ctrl, pq, r, pend);
+        flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
+        stats.add(visits);
+    };
+    // Ray costs differ a lot, so the last quarter of the rays is handed out in batches of 32 from a shared cursor and
+    // evens out what the fixed stride over the first three quarters left uneven.  (All rays from the cursor costs
+    // one same-address atomic per 32 rays: 0.07 ms at 1080p, a third of this kernel there.)  The next batch is
+    // reserved before the current one is walked, so the atomic's latency hides behind the walk.
+    const uint32_t n_fixed = (n_rays - n_rays / 4u) & ~31u;
+    const uint32_t warps = gridDim.x * (kBlock / 32);
+    for (uint32_t base = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * 32u; base < n_fixed; base += warps * 32u) walk_batch(base);
+    uint32_t base = 0;
+    if (lane == 0) base = n_fixed + atomicAdd(&ctrl->trav_cursor, 32u);
+    base = __shfl_sync(kFull, base, 0);
+    while (base < n_rays) {
+        uint32_t next = 0;
+        if (lane == 0) next = n_fixed + atomicAdd(&ctrl->trav_cursor, 32u);
+        walk_batch(base);
+        base = __shfl_sync(kFull, next, 0);
     }
+    stats.commit(ctrl);
+}
+
+// Spill round `round` (1..kSpillRounds): walks the (ray, subtree) entries the previous round handed over, one per
+// thread, breadth first under the node budget, except the last round, which finishes whatever is left.  Entries are short by construction, so a fixed
+// stride is enough here.
+__global__ void __launch_bounds__(kBlock, 6) k_traverse_spill(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                              const __grid_constant__ WaveBuffers wb, int wave, int round) {
+    __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
+    WaveCtrl* ctrl = &wb.ctrl[wave];
+    const int pq = wave & 1;
+    const uint2* in = wb.spill[(round - 1) & 1];
+    uint2* out = wb.spill[round & 1];
+    const uint32_t n_in = min(ctrl->spill_count[round - 1], wb.spill_capacity);
+    const uint32_t n_round = (n_in + 31u) & ~31u;
+    const bool last = round >= kSpillRounds;
+    VisitStats stats;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        Pending pend;
+        pend.n = 0;
+#pragma unroll
+        for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
+        uint32_t visits = 0, r = 0;
+        if (i < n_in) {
+            const uint2 e = in[i];
+            if (e.x != 0xFFFFFFFFu) {
+                r = e.x;
+                const V3 o = ld3(wb.ray_o[pq][r]), d = ld3(wb.ray_d[pq][r]);
+                const V3 oo = xform_point_3x4(sc.aabb_w2o, o), dd = xform_vector_3x4(sc.aabb_w2o, d);
+                const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
+                const float tcur = wb.ray_tcur[r];
+                if (last) visits = walk_tree<kWalkDepthFirst>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, nullptr, nullptr, pend);
+                else visits = walk_tree<kWalkBreadthFirst>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, out, &ctrl->spill_count[round], pend);
+            }
+        }
+        flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
+        stats.add(visits);
+    }
+    stats.commit(ctrl);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -441,12 +555,24 @@ int grid_for(uint32_t n_items, int blocks_per_sm) {
     return (int)(need < 1 ? 1 : (need < cap ? need : cap));
 }
 
+// Blocks of `kernel` one SM holds at once: grid-stride and cursor-fed kernels are launched as exactly one resident
+// wave of blocks (a partial second wave of a fixed-stride grid left SMs idle 40 % of the walk kernel's time).
+int resident_blocks(const void* kernel) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kBlock, 0) != cudaSuccess || n < 1) n = 4;
+    return n;
+}
+
 int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
-    if (wave == 1) k_traverse<true><<<grid_for(upper, 8), kBlock, 0, s>>>(sc, pp, wb, wave);
-    else k_traverse<false><<<grid_for(upper, 8), kBlock, 0, s>>>(sc, pp, wb, wave);
-    return 1;
+    static const int per_sm_primary = resident_blocks((const void*)k_traverse<true>), per_sm_secondary = resident_blocks((const void*)k_traverse<false>);
+    if (wave == 1) k_traverse<true><<<grid_for(upper, per_sm_primary), kBlock, 0, s>>>(sc, pp, wb, wave);
+    else k_traverse<false><<<grid_for(upper, per_sm_secondary), kBlock, 0, s>>>(sc, pp, wb, wave);
+    if (!pp.spill_budget) return 1;
+    static const int per_sm_spill = resident_blocks((const void*)k_traverse_spill);
+    for (int round = 1; round <= kSpillRounds; round++) k_traverse_spill<<<sm_count() * per_sm_spill, kBlock, 0, s>>>(sc, pp, wb, wave, round);
+    return 1 + kSpillRounds;
 }
 
 // GPRT_ISECT_VARIANT=-1 (profiling aid): with GPRT_PER_TYPE_LAUNCHES=1, run the one-candidate-per-thread kernels, which
@@ -525,12 +651,14 @@ int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb,
 
 int launch_shade_spawn(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
     const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
-    k_shade_spawn<<<grid_for(upper, 8), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, wave);
+    static const int per_sm = resident_blocks((const void*)k_shade_spawn);
+    k_shade_spawn<<<grid_for(upper, per_sm), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, wave);
     return 1;
 }
 
 int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, const OutputBuffers& ob, void* stream) {
-    k_final_color<<<grid_for(pp.n_pixels, 8), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
+    static const int per_sm = resident_blocks((const void*)k_final_color);
+    k_final_color<<<grid_for(pp.n_pixels, per_sm), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
     return 1;
 }
 

@@ -60,6 +60,8 @@ struct SceneDev {
     Material plane_mat;
 };
 
+constexpr int kSpillRounds = 3; // traversal hand-over rounds after the main walk (the last one has no node budget)
+
 struct WaveCtrl { // one per wave, zeroed at the start of a pass
     uint32_t n_rays;
     uint32_t n_radiance, n_shadow;
@@ -70,7 +72,9 @@ struct WaveCtrl { // one per wave, zeroed at the start of a pass
     uint32_t work[kNumTypes];   // per type: analytic tests / metaball march steps / SDF distance evaluations
     uint32_t max_evals[kNumTypes];      // profiling: most field evaluations spent on one candidate
     uint32_t evals_hist[kNumTypes][12]; // profiling: candidates by floor(log2(evaluations)) (bin 0: none)
-    uint32_t _pad[1];
+    uint32_t trav_cursor;       // next unclaimed ray of the wave's traversal (warps claim batches)
+    uint32_t node_visits, max_node_visits; // LBVH nodes fetched by the wave; by its longest ray
+    uint32_t spill_count[kSpillRounds];    // (ray, subtree) entries handed to spill round i + 1
 };
 
 struct PassParams {
@@ -81,6 +85,7 @@ struct PassParams {
     uint32_t ray_capacity;                   // 2 * n_pixels
     uint32_t cand_capacity;                  // per type
     uint32_t brute_force;
+    uint32_t spill_budget;                   // node fetches per thread before a walk is handed on; 0 = never (small scenes)
     // multi-GPU row striping: with stripe_world > 1 the pass covers LOCAL rows tile_y .. tile_y+tile_h of
     // rank stripe_rank, local row l being global row ((l / stripe_rows) * stripe_world + stripe_rank) *
     // stripe_rows + l % stripe_rows.  DispatchRaysIndex / Dimensions stay global either way.
@@ -102,6 +107,8 @@ struct WaveBuffers {
     uint2* cand[kNumTypes];      // (ray slot, primitive)
     float4* cand_res[kNumTypes]; // world normal xyz, w = t (or -1: no hit)
     WaveCtrl* ctrl;    // [kMaxDepth + 1]
+    uint2* spill[2];   // traversal hand-over queues (ray slot, subtree root), ping-pong by round
+    uint32_t spill_capacity;
     // per-level, per-pixel hit records: index (level - 1) * n_pixels + pixel
     float4* lvl_o_t;   // ray origin xyz, committed t
     float4* lvl_d;     // ray direction xyz

@@ -168,6 +168,8 @@ typedef struct gprt_wave_stats {
     uint32_t work[10];
     uint32_t max_evals[10];
     uint32_t evals_hist[10][12]; /* candidates by floor(log2(field evaluations)) + 1; bin 0 = none */
+    uint32_t node_visits;        /* LBVH nodes fetched by the wave's traversal (first band)            */
+    uint32_t max_node_visits;    /* ... by its single longest ray: the traversal's serial critical path */
 } gprt_wave_stats;
 
 typedef struct gprt_timing {

@@ -38,7 +38,7 @@ def main():
         depth = r.scene().config.max_recursion_depth
         for w in range(1, depth + 1):
             s = r.wave_stats(w)
-            out[f"wave{w}"] = {"radiance": s.n_radiance, "shadow": s.n_shadow,
+            out[f"wave{w}"] = {"radiance": s.n_radiance, "shadow": s.n_shadow, "node_visits": s.node_visits, "max_node_visits": s.max_node_visits,
                                "types": {TNAMES[t]: {"cand": s.candidates[t], "work": s.work[t], "max": s.max_evals[t], "hist": list(s.evals_hist[t])}
                                          for t in range(10) if s.candidates[t]}}
     print(json.dumps(out))
