@@ -9,8 +9,10 @@ procedural scene, 1920x1080, depth 3; elapsed_time advances 1/60 s per step so e
 per-frame transforms).  `value` = rays traced (radiance + shadow, counted on the device) per
 second with the scene resident in HBM and the output left in HBM; `e2e` = the same through the
 host-facing call (host scene constants in, host RGBA8 frame out, copies inside the timed region).
-N > 1: one process per GPU (torchrun), the frame is sharded by interleaved row stripes, every rank
-renders its stripes and rank 0 gathers the RGBA8 rows over NCCL (strong scaling: total work fixed).
+N > 1: one process per GPU (torchrun).  The 8K config is sharded by interleaved row stripes: every rank
+renders its stripes of every frame and rank 0 gathers the RGBA8 rows over NCCL (strong scaling: total
+work fixed).  The 1080p configs are sharded by frames (frame g on rank g % N, gathered to rank 0; a step
+is N frames, weak scaling): a 2 ms frame has a 1.5 ms serial floor and cannot be split 8 ways.
 `--impl reference` times the reference's own shader code on the host cores (oracle/_ref).
 """
 import argparse
@@ -116,41 +118,58 @@ def run_gpu(args):
     cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0  # the scene's own
     r = Renderer(scene_id=conf["scene_id"], device=local_rank, config=cfg)
     r.on_init()
-    r.create_frame_contexts()  # 3 frames in flight, like the reference's frame_count (src/Renderer.h:92)
     W, H = r.width, r.height
+    # N > 1: "frames" = every rank renders whole frames (frame g on rank g % N), "stripes" = every rank renders its row
+    # stripes of every frame.  A frame has a serial floor (3 waves x the longest ray's dependent chain, ~1.5 ms at any
+    # size), so a 2 ms frame cannot be split 8 ways, while a 50 ms one can: frames for the small configs, stripes for 8K.
+    mode = "single" if world == 1 else (args.multi_gpu if args.multi_gpu != "auto" else ("frames" if W * H <= (1 << 22) else "stripes"))
+    n_slots = args.frames_in_flight or (min(8, 2 + world) if mode == "stripes" else 3)
+    r.set_frame_count(n_slots)  # the reference has frame_count = 3 (src/Renderer.h:92); a GPU that renders only a stripe needs more to hide a frame's serial tail
+    r.create_frame_contexts()
+    frames_per_step = world if mode == "frames" else 1
+
+    def frame_time(i):
+        """elapsed_time of this rank's frame of step i"""
+        return ((i * world + rank) if mode == "frames" else i) / 60.0
     n_prims = len(r.scene().aabbs)
     main = torch.cuda.current_stream()
-    n_slots = 3
     ext = [torch.cuda.ExternalStream(r.frame_stream(j), device=dev) for j in range(n_slots)]
 
-    srows = multigpu.stripe_rows_for(H, world)
-    pad_rows = multigpu.max_local_rows(H, srows, world) if world > 1 else H
+    srows = multigpu.stripe_rows_for(H, world) if mode == "stripes" else H
+    pad_rows = multigpu.max_local_rows(H, srows, world) if mode == "stripes" else H
     local = [torch.empty((pad_rows, W, 4), dtype=torch.uint8, device=dev) for _ in range(n_slots)]
-    gathered = [[torch.empty_like(local[0]) for _ in range(world)] if (world > 1 and rank == 0) else None for _ in range(n_slots)]
-    full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else local[j] for j in range(n_slots)]
-    host = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(n_slots)] if rank == 0 else [None] * n_slots
+    # rank 0: one contiguous [world, rows, W, 4] block per slot, so that the frames of a step leave in one D2H copy
+    blocks = [torch.empty((world, pad_rows, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None for _ in range(n_slots)]
+    gathered = [list(b.unbind(0)) if b is not None else None for b in blocks]
+    full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (mode == "stripes" and rank == 0) else local[j] for j in range(n_slots)]
+    host = [torch.empty((frames_per_step, H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(n_slots)] if rank == 0 else [None] * n_slots
     flush = [torch.empty(192 << 20, dtype=torch.uint8, device=dev) for _ in range(n_slots)]  # each > the 126 MB L2
 
     def step(i, to_host, flush_l2):
         """One step = one frame: update (host), [L2 flush], dispatch, [gather + compose on rank 0], [D2H].  Asynchronous:
-        frame i runs on frame slot i % 3 (own context, own stream); the *_async call first waits for that slot's previous frame."""
+        frame i runs on frame slot i % n_slots (own context, own stream); the *_async call first waits for that slot's previous frame."""
         j = r.next_frame_slot()
-        r.on_update(i / 60.0)
+        r.on_update(frame_time(i))
         with torch.cuda.stream(ext[j]):
             if flush_l2:
                 flush[j].zero_()
-            if world == 1:
+            if mode == "single":
                 if to_host:
                     r.on_render_async(host[j].data_ptr())  # host scene constants in, pinned host frame out
                 else:
                     r.do_raytracing_async(local[j].data_ptr())
+            elif mode == "frames":
+                r.do_raytracing_async(local[j].data_ptr())
+                multigpu.gather_frames(local[j], gathered[j], dst=0)  # frame i * N + k from rank k
+                if rank == 0 and to_host:
+                    host[j].copy_(blocks[j], non_blocking=True)
             else:
                 r.do_raytracing_striped_async(local[j].data_ptr(), srows, rank, world)
                 multigpu.gather_stripes(local[j], gathered[j], dst=0)
                 if rank == 0:
                     multigpu.compose(full[j], gathered[j], H, srows, world)
                     if to_host:
-                        host[j].copy_(full[j], non_blocking=True)
+                        host[j][0].copy_(full[j], non_blocking=True)
 
     def barrier():
         if world > 1:
@@ -191,15 +210,18 @@ def run_gpu(args):
         """Strictly serial: one blocking frame at a time (no frames in flight), L2 flushed before each, per-frame CUDA events."""
         total = 0.0
         for i in range(steps):
-            r.on_update((first_step + i) / 60.0)
+            r.on_update(frame_time(first_step + i))
             flush[0].zero_()
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(main)
             with torch.cuda.stream(ext[0]):
                 ext[0].wait_event(e0)
-                if world == 1:
+                if mode == "single":
                     r.do_raytracing(local[0].data_ptr())
+                elif mode == "frames":
+                    r.do_raytracing(local[0].data_ptr())
+                    multigpu.gather_frames(local[0], gathered[0], dst=0)
                 else:
                     r.do_raytracing_striped(local[0].data_ptr(), srows, rank, world)
                     multigpu.gather_stripes(local[0], gathered[0], dst=0)
@@ -215,8 +237,8 @@ def run_gpu(args):
         """Rays traced (device counters) by exactly the frames of the timed passes (untimed, synchronous)."""
         rays = 0
         for i in range(steps):
-            r.on_update((first_step + i) / 60.0)
-            if world == 1:
+            r.on_update(frame_time(first_step + i))
+            if mode != "stripes":
                 r.do_raytracing(local[0].data_ptr())
             else:
                 r.do_raytracing_striped(local[0].data_ptr(), srows, rank, world)
@@ -248,26 +270,31 @@ def run_gpu(args):
     result = None
     if rank == 0:
         value = rays / (dev_ms * 1e-3) / 1e6
-        par = "1 GPU" if world == 1 else f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, NCCL gather of the RGBA8 rows to rank 0"
+        par = {"single": "1 GPU",
+               "frames": f"{world} GPUs, whole frames round-robin (frame g on rank g % {world}), replicated scene, NCCL gather of the RGBA8 frames to rank 0; "
+                         f"a step is {world} frames, one per rank",
+               "stripes": f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, NCCL gather of the RGBA8 rows to rank 0"}[mode]
         result = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "weak" if mode == "frames" else "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": conf["workload"], "width": W, "height": H, "math_mode": args.math,
-                       "frames_in_flight": n_slots,
+                       "frames_in_flight": n_slots, "multi_gpu": mode, "frames_per_step": frames_per_step,
                        "l2_flush": "192 MiB memset on the frame's stream before every timed step (and the 0.6 GB wavefront state of a frame exceeds L2)",
                        "timing": "CUDA events ordered around all frame streams, exactly K steps between barriers, max over ranks",
                        "parallelism": par},
-            "primary_mrays_per_s": round(W * H * args.steps / (dev_ms * 1e-3) / 1e6, 3),
+            "frame_ms": round(dev_ms / args.steps / frames_per_step, 4),
+            "primary_mrays_per_s": round(W * H * frames_per_step * args.steps / (dev_ms * 1e-3) / 1e6, 3),
             "rays_per_step": rays // args.steps,
             "single_frame_ms": round(lat_ms, 4),
             "single_frame_how": "one frame at a time (nothing in flight), L2 flushed, CUDA events per frame: the latency of a 1080p frame",
             "e2e": {"value": round(rays / (e2e_ms * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "h2d_bytes_per_step": 136 + (0 if r.uses_device_transforms() else 128 * n_prims), "d2h_bytes_per_step": W * H * 4,
+                    "h2d_bytes_per_step": 136 + (0 if r.uses_device_transforms() else 128 * n_prims), "d2h_bytes_per_step": W * H * 4 * frames_per_step,
                     "transforms": "computed on the GPU (gprt_update_transforms)" if r.uses_device_transforms() else "computed on the host, uploaded every step",
-                    "how": "Renderer.on_update + on_render_async per step (public API, 3 frames in flight): host scene constants in, pinned host "
+                    "how": f"Renderer.on_update + on_render_async per step (public API, {n_slots} frames in flight): host scene constants in, pinned host "
                            "RGBA8 frame out every step; max(CUDA events, host wall clock) around all steps + wait_for_gpu"
-                           + ("" if world == 1 else "; stripes gathered to rank 0 over NCCL, composed, then copied to the host")},
+                           + {"single": "", "frames": "; every step's frames gathered to rank 0 over NCCL, then copied to the host in one block",
+                              "stripes": "; stripes gathered to rank 0 over NCCL, composed, then copied to the host"}[mode]},
             "gpu_launches": launches_per_step * (3 * args.steps + min(args.steps, 10)),
             "clocks": clocks,
         }
@@ -277,7 +304,7 @@ def run_gpu(args):
     # free every tensor that was used on the frame streams BEFORE the contexts (and their streams) are destroyed:
     # the caching allocator records an event on those streams when such a block is released
     barrier()
-    del local, gathered, full, host, flush
+    del local, gathered, blocks, full, host, flush
     import gc
     gc.collect()
     torch.cuda.synchronize()
@@ -432,6 +459,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gprt", choices=["gprt", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--frames-in-flight", type=int, default=0, help="frame slots (contexts + streams); 0 = 3 on one GPU, min(8, 2 + N) on N")
+    ap.add_argument("--multi-gpu", default="auto", choices=["auto", "frames", "stripes"],
+                    help="N > 1: whole frames round-robin over the ranks, or row stripes of every frame; auto = frames up to 4 Mpixel, stripes above")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development runs of the large configs)")
     ap.add_argument("--math", default=os.environ.get("GPRT_BENCH_MATH", "parity"), choices=["parity", "fast"])
     args = ap.parse_args()

@@ -132,6 +132,8 @@ def lib():
         "gprt_renderer_do_raytracing_async": (i32, [vp, vp]),
         "gprt_renderer_do_raytracing_stripes_async": (i32, [vp, u32, u32, u32, vp]),
         "gprt_renderer_create_frame_contexts": (i32, [vp]),
+        "gprt_renderer_set_frame_count": (i32, [vp, i32]),
+        "gprt_renderer_get_frame_count": (i32, [vp]),
         "gprt_renderer_set_device_transforms": (i32, [vp, i32]),
         "gprt_renderer_get_device_transforms": (i32, [vp]),
         "gprt_set_animation": (i32, [vp, vp, u32]),
@@ -161,7 +163,7 @@ EXPORTED_SYMBOLS = [
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
     "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_render_async", "gprt_renderer_do_raytracing_async",
-    "gprt_renderer_do_raytracing_stripes_async", "gprt_renderer_create_frame_contexts", "gprt_renderer_set_device_transforms", "gprt_renderer_get_device_transforms", "gprt_renderer_next_frame_slot",
+    "gprt_renderer_do_raytracing_stripes_async", "gprt_renderer_create_frame_contexts", "gprt_renderer_set_frame_count", "gprt_renderer_get_frame_count", "gprt_renderer_set_device_transforms", "gprt_renderer_get_device_transforms", "gprt_renderer_next_frame_slot",
     "gprt_set_animation", "gprt_update_transforms", "gprt_get_transforms",
     "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_get_size", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",

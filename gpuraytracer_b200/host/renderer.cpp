@@ -48,7 +48,7 @@ int Renderer::prepare_transforms(gprt_ctx* c, const gprt_prim_per_frame** per_fr
 Renderer::~Renderer() { on_destroy(); }
 
 void Renderer::on_destroy() {
-    for (int i = 1; i < kFrameCount; i++)
+    for (int i = 1; i < kMaxFrameCount; i++)
         if (m_frame_ctx[i]) { gprt_sync(m_frame_ctx[i]); gprt_destroy(m_frame_ctx[i]); m_frame_ctx[i] = nullptr; }
     m_frame_ctx[0] = nullptr;
     if (m_ctx) {
@@ -59,11 +59,22 @@ void Renderer::on_destroy() {
     m_initialized = false;
 }
 
-// Frame slots 1..2 are created on first use: same geometry, shader table and (deterministic) LBVH.
+int Renderer::set_frame_count(int n) {
+    if (n < 1 || n > kMaxFrameCount) return GPRT_E_INVALID_ARG;
+    const int rc = wait_for_gpu();
+    if (rc != GPRT_OK) return rc;
+    for (int i = n; i < kMaxFrameCount; i++)
+        if (i > 0 && m_frame_ctx[i]) { gprt_destroy(m_frame_ctx[i]); m_frame_ctx[i] = nullptr; }
+    m_frame_count = n;
+    m_frame_index = 0;
+    return GPRT_OK;
+}
+
+// Frame slots 1.. are created on first use: same geometry, shader table and (deterministic) LBVH.
 int Renderer::ensure_frame_contexts() {
     if (!m_initialized) return m_device < 0 ? GPRT_E_NO_DEVICE : GPRT_E_NOT_BUILT;
     m_frame_ctx[0] = m_ctx;
-    for (int i = 1; i < kFrameCount; i++) {
+    for (int i = 1; i < m_frame_count; i++) {
         if (m_frame_ctx[i]) continue;
         gprt_ctx* saved = m_ctx;
         int rc = gprt_create(&m_ctx, m_device, &m_scene.config);
@@ -79,7 +90,7 @@ int Renderer::ensure_frame_contexts() {
 int Renderer::on_render_async(void* h_rgba8_pinned) {
     int rc = ensure_frame_contexts();
     if (rc != GPRT_OK) return rc;
-    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    gprt_ctx* c = m_frame_ctx[m_frame_index % (uint32_t)m_frame_count];
     m_frame_index++;
     rc = gprt_sync(c); // this slot's previous frame (its staging, queues and host buffer) must be done
     if (rc != GPRT_OK) return rc;
@@ -94,7 +105,7 @@ int Renderer::on_render_async(void* h_rgba8_pinned) {
 int Renderer::do_raytracing_async(void* d_rgba8) {
     int rc = ensure_frame_contexts();
     if (rc != GPRT_OK) return rc;
-    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    gprt_ctx* c = m_frame_ctx[m_frame_index % (uint32_t)m_frame_count];
     m_frame_index++;
     rc = gprt_sync(c);
     if (rc != GPRT_OK) return rc;
@@ -109,7 +120,7 @@ int Renderer::do_raytracing_async(void* d_rgba8) {
 int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
     int rc = ensure_frame_contexts();
     if (rc != GPRT_OK) return rc;
-    gprt_ctx* c = m_frame_ctx[m_frame_index % kFrameCount];
+    gprt_ctx* c = m_frame_ctx[m_frame_index % (uint32_t)m_frame_count];
     m_frame_index++;
     rc = gprt_sync(c);
     if (rc != GPRT_OK) return rc;
@@ -124,13 +135,13 @@ int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, u
 int Renderer::wait_for_gpu() {
     int rc = GPRT_OK;
     if (m_ctx) rc = gprt_sync(m_ctx);
-    for (int i = 1; i < kFrameCount; i++)
+    for (int i = 1; i < kMaxFrameCount; i++)
         if (m_frame_ctx[i]) { const int r2 = gprt_sync(m_frame_ctx[i]); if (rc == GPRT_OK) rc = r2; }
     return rc;
 }
 
 gprt_ctx* Renderer::frame_context(int slot) {
-    if (slot < 0 || slot >= kFrameCount) return nullptr;
+    if (slot < 0 || slot >= m_frame_count) return nullptr;
     return slot == 0 ? m_ctx : m_frame_ctx[slot];
 }
 
@@ -272,6 +283,8 @@ int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_
 int gprt_renderer_get_device_transforms(gprt_renderer* r) { return r && r->impl.device_transforms() ? 1 : 0; }
 int gprt_renderer_set_device_transforms(gprt_renderer* r, int on) { if (!r) return GPRT_E_INVALID_ARG; r->impl.set_device_transforms(on != 0); return GPRT_OK; }
 int gprt_renderer_create_frame_contexts(gprt_renderer* r) { return r ? r->impl.create_frame_contexts() : GPRT_E_INVALID_ARG; }
+int gprt_renderer_set_frame_count(gprt_renderer* r, int n) { return r ? r->impl.set_frame_count(n) : GPRT_E_INVALID_ARG; }
+int gprt_renderer_get_frame_count(gprt_renderer* r) { return r ? r->impl.frame_count() : -1; }
 int gprt_renderer_next_frame_slot(gprt_renderer* r) { return r ? r->impl.next_frame_slot() : -1; }
 int gprt_renderer_wait_for_gpu(gprt_renderer* r) { return r ? r->impl.wait_for_gpu() : GPRT_E_INVALID_ARG; }
 gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot) { return r ? r->impl.frame_context(slot) : nullptr; }

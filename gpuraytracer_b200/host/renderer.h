@@ -31,7 +31,11 @@ public:
     int do_raytracing_async(void* d_rgba8);                      // same with device output
     int do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8); // multi-GPU, 3 in flight
     int create_frame_contexts() { return ensure_frame_contexts(); }
-    int next_frame_slot() const { return (int)(m_frame_index % kFrameCount); }
+    int next_frame_slot() const { return (int)(m_frame_index % (uint32_t)m_frame_count); }
+    // Frames in flight: 3 like the reference unless changed (1..kMaxFrameCount).  More slots hide the serial tail of a
+    // frame better when a GPU renders only a stripe of it; each slot owns a full set of wavefront queues.
+    int set_frame_count(int n);
+    int frame_count() const { return m_frame_count; }
     int wait_for_gpu();                                          // DeviceResources::wait_for_gpu: all frames done
     gprt_ctx* frame_context(int slot);
     float primary_mrays_per_s();                                 // calculate_frame_stats, :375-399
@@ -53,10 +57,12 @@ private:
     int build_acceleration_structures();       // :788-835  -> gprt_build_accel
 
     SceneState m_scene;
-    static constexpr int kFrameCount = 3;
+    static constexpr int kFrameCount = 3;     // src/Renderer.h:92
+    static constexpr int kMaxFrameCount = 8;
+    int m_frame_count = kFrameCount;
     int ensure_frame_contexts();
     gprt_ctx* m_ctx = nullptr;           // frame slot 0 (and the synchronous path)
-    gprt_ctx* m_frame_ctx[kFrameCount] = {nullptr, nullptr, nullptr};
+    gprt_ctx* m_frame_ctx[kMaxFrameCount] = {};
     uint32_t m_frame_index = 0;
     int m_device = -1;
     int prepare_transforms(gprt_ctx* c, const gprt_prim_per_frame** per_frame, uint32_t* n);

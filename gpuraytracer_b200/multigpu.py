@@ -1,4 +1,4 @@
-"""Tile sharding of one frame across the GPUs of a box.
+"""Sharding of the path across the GPUs of a box: row stripes of one frame, or whole frames.
 
 The path shards by pixels: the scene is replicated (every rank builds the same LBVH from the same
 inputs), rank r renders the row stripes r, r + world, ... (gprt_dispatch_stripes) and the RGBA8 rows
@@ -46,6 +46,18 @@ def gather_stripes(local, gathered, dst=0, group=None):
     to rank `dst`.  `gathered` is a list of world tensors on dst, None elsewhere."""
     import torch.distributed as dist
     dist.gather(local, gathered if dist.get_rank(group) == dst else None, dst=dst, group=group)
+
+
+def frame_owner(frame: int, world: int) -> int:
+    """Frame sharding (small frames: a frame's serial floor does not shrink with its pixel count, so
+    whole frames are dealt round-robin instead of stripes of each): rank that renders global frame `frame`."""
+    return int(frame) % max(int(world), 1)
+
+
+def gather_frames(local, gathered, dst=0, group=None):
+    """Gather the whole frame every rank rendered this step to rank `dst`: gathered[k] is global frame
+    step * world + k.  Same collective as gather_stripes."""
+    gather_stripes(local, gathered, dst=dst, group=group)
 
 
 def compose(full, gathered, height: int, stripe_rows: int, world: int):

@@ -114,6 +114,14 @@ class Renderer:
     def create_frame_contexts(self):
         check(self._lib.gprt_renderer_create_frame_contexts(self._h), "create_frame_contexts")
 
+    def set_frame_count(self, n: int):
+        """Frames in flight for the *_async calls (default 3 = the reference's frame_count, src/Renderer.h:92)."""
+        check(self._lib.gprt_renderer_set_frame_count(self._h, int(n)), "set_frame_count")
+
+    @property
+    def frame_count(self) -> int:
+        return int(self._lib.gprt_renderer_get_frame_count(self._h))
+
     def next_frame_slot(self) -> int:
         return int(self._lib.gprt_renderer_next_frame_slot(self._h))
 

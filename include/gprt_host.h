@@ -70,8 +70,11 @@ int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_
  * Default: on for scenes of >= 4096 primitives. */
 int gprt_renderer_set_device_transforms(gprt_renderer* r, int on);
 int gprt_renderer_get_device_transforms(gprt_renderer* r);
-int gprt_renderer_create_frame_contexts(gprt_renderer* r); /* create the 3 frame contexts (and their streams) up front */
-int gprt_renderer_next_frame_slot(gprt_renderer* r);       /* slot (0..2) the next *_async call will use */
+/* Frames in flight: 3 like the reference (src/Renderer.h:92) unless set (1..8); waits for the GPU, restarts at slot 0. */
+int gprt_renderer_set_frame_count(gprt_renderer* r, int n);
+int gprt_renderer_get_frame_count(gprt_renderer* r);
+int gprt_renderer_create_frame_contexts(gprt_renderer* r); /* create the frame contexts (and their streams) up front */
+int gprt_renderer_next_frame_slot(gprt_renderer* r);       /* slot the next *_async call will use */
 int gprt_renderer_wait_for_gpu(gprt_renderer* r);
 gprt_ctx* gprt_renderer_frame_context(gprt_renderer* r, int slot); /* NULL until the slot was used */
 int gprt_renderer_on_size_changed(gprt_renderer* r, uint32_t width, uint32_t height);

@@ -85,6 +85,39 @@ def test_gather_and_compose_over_gloo(tmp_path, world, height_crop, srows):
     np.testing.assert_array_equal(np.load(out), golden)
 
 
+def _frames_worker(rank, world, port, steps, out_path):
+    import torch
+    import torch.distributed as dist
+    from gpuraytracer_b200 import multigpu as mg
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    order = []
+    for step in range(steps):
+        g = step * world + rank  # the global frame this rank renders in this step
+        assert mg.frame_owner(g, world) == rank
+        local = torch.full((4, 6, 4), g, dtype=torch.uint8)  # stands in for the rendered frame
+        gathered = [torch.zeros_like(local) for _ in range(world)] if rank == 0 else None
+        mg.gather_frames(local, gathered, dst=0)
+        if rank == 0:
+            order += [int(f[0, 0, 0]) for f in gathered]
+            assert all(bool((f == f[0, 0, 0]).all()) for f in gathered)
+    if rank == 0:
+        np.save(out_path, np.array(order))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_frame_sharding_delivers_frames_in_order_over_gloo(tmp_path, world):
+    """Frame sharding (bench.py, 1080p configs at N > 1): frame g is rendered by rank g % N and rank 0 receives
+    the frames of every step in global order."""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "order.npy")
+    mp.spawn(_frames_worker, args=(world, _free_port(), 4, out), nprocs=world, join=True)
+    np.testing.assert_array_equal(np.load(out), np.arange(4 * world))
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,srows,height", [(2, 8, 180), (4, 5, 180), (8, 3, 181), (3, 7, 90)])
 def test_striped_dispatch_equals_full_frame(world, srows, height):
