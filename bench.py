@@ -250,6 +250,9 @@ def run_gpu(args):
             rays = int(t.item())
         return rays
 
+    # every frame slot allocates its wavefront queues on first use: prime all of them before the W warm-up steps
+    for i in range(n_slots):
+        step(i, True, True)
     for i in range(args.warmup):
         step(i, False, True)
     for i in range(args.warmup):
@@ -295,7 +298,7 @@ def run_gpu(args):
                            "RGBA8 frame out every step; max(CUDA events, host wall clock) around all steps + wait_for_gpu"
                            + {"single": "", "frames": "; every step's frames gathered to rank 0 over NCCL, then copied to the host in one block",
                               "stripes": "; stripes gathered to rank 0 over NCCL, composed, then copied to the host"}[mode]},
-            "gpu_launches": launches_per_step * (3 * args.steps + min(args.steps, 10)),
+            "gpu_launches": launches_per_step * (2 * args.steps + min(args.steps, 10)),  # the two timed passes + the single-frame latency pass
             "clocks": clocks,
         }
         result["roofline"], result["roofline_hbm"], result["kernel_ms"] = roofline(args, conf, local_rank, cfg, world)
