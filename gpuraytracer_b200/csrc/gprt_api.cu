@@ -48,6 +48,7 @@ struct gprt_ctx {
     // device scene
     float* d_aabbs = nullptr;
     PrimRecord* d_prims = nullptr;
+    uint32_t spill_capacity_limit = 0; // GPRT_SPILL_CAPACITY (tests: forces the queue-full fallback of the walk)
     uint32_t spill_budget = 0;         // LBVH node fetches per thread before a walk is handed to the next spill round
     uint8_t* d_prim_types = nullptr;   // type id per primitive, tagged into the LBVH leaf refs
     float* d_per_frame = nullptr;
@@ -180,6 +181,7 @@ int ensure_pass_buffers(gprt_ctx* c, uint32_t pixels) {
     A(c->wb.ctrl, (size_t)(kMaxDepth + 2));
     A(c->wb.spill[0], P); A(c->wb.spill[1], P);
     c->wb.spill_capacity = (uint32_t)P;
+    if (c->spill_capacity_limit && c->spill_capacity_limit < c->wb.spill_capacity) c->wb.spill_capacity = c->spill_capacity_limit; // test hook
     A(c->wb.lvl_o_t, P * depth);
     A(c->wb.lvl_d, P * depth);
     A(c->wb.lvl_n, P * depth);
@@ -389,6 +391,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : kernels_parity();
     { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
     { const char* e = getenv("GPRT_SPILL_BUDGET"); c->spill_budget = e ? (uint32_t)atoi(e) : kSpillBudget; } // tuning aid
+    { const char* e = getenv("GPRT_SPILL_CAPACITY"); c->spill_capacity_limit = e ? (uint32_t)atoi(e) : 0u; }
     std::memset(&c->scene, 0, sizeof c->scene);
     std::memset(&c->wb, 0, sizeof c->wb);
     std::memset(c->h_instances, 0, sizeof c->h_instances);

@@ -133,6 +133,37 @@ def test_config5_lbvh_equals_brute_force_and_oracle():
     check(oracle_render(scene), a_img, a_ids)
 
 
+@pytest.mark.parametrize("budget,capacity", [("8", None), ("8", "1000"), ("1", None), ("0", None)])
+def test_traversal_spill_rounds_do_not_change_the_candidates(monkeypatch, budget, capacity):
+    """The walk hands long rays over to spill rounds after a node budget (kernels.cu, walk_tree).  Whatever the
+    budget -- a tiny one sends nearly every ray through all three rounds, 0 disables the rounds -- and even when
+    the hand-over queue is full (capacity hook: the walk then finishes in place), the candidate set, image and hit
+    ids are those of the brute-force loop."""
+    monkeypatch.setenv("GPRT_SPILL_BUDGET", budget)
+    if capacity:
+        monkeypatch.setenv("GPRT_SPILL_CAPACITY", capacity)
+    a_img, a_ids, scene, a_c, _ = gpu_render(5, 480, 270, 1.0, grid_n=96)  # 9216 primitives: spill rounds are on from 4096
+    assert len(scene.aabbs) == 96 * 96
+    monkeypatch.delenv("GPRT_SPILL_BUDGET")
+    monkeypatch.delenv("GPRT_SPILL_CAPACITY", raising=False)
+    b_img, b_ids, _, b_c, _ = gpu_render(5, 480, 270, 1.0, grid_n=96, flags=GPRT_FLAG_BRUTE_FORCE_TRAVERSAL)
+    np.testing.assert_array_equal(a_img, b_img)
+    np.testing.assert_array_equal(a_ids, b_ids)
+    assert list(a_c.candidates) == list(b_c.candidates)
+
+
+def test_traversal_node_budget_bounds_the_longest_walk():
+    """gprt_get_wave_stats: with the spill rounds no thread fetches more than the node budget (64) on one entry."""
+    with Renderer(scene_id=5, width=960, height=540, grid_n=256, device=0, config=make_cfg()) as r:
+        r.on_init()
+        r.on_update(1.0)
+        r.on_render()
+        for wave in (1, 2, 3):
+            s = r.wave_stats(wave)
+            assert s.node_visits > 0
+            assert 0 < s.max_node_visits <= 64, (wave, s.max_node_visits)
+
+
 def test_config5_million_primitives_tile():
     """BASELINE config 5 at full scale (1000 x 1000 grid, 7680 x 4320 dispatch): one tile, LBVH vs
     brute force bit-identical, and parity against the oracle (host BVH) on the same tile."""
