@@ -41,9 +41,8 @@ struct gprt_ctx {
     std::vector<gprt_vertex> h_vertices;
     std::vector<uint16_t> h_indices;
     std::vector<gprt_hit_group_record> h_records;
-    gprt_instance_desc h_instances[2];
+    std::vector<gprt_instance_desc> h_tri_insts, h_aabb_insts; // TLAS instances per BLAS kind, in TLAS order
     bool have_tri_instance = false, have_aabb_instance = false, have_geometry = false, have_table = false;
-    uint32_t tri_contrib = 0, aabb_contrib = 2;
 
     // device scene
     float* d_aabbs = nullptr;
@@ -58,6 +57,9 @@ struct gprt_ctx {
     uint32_t n_anim = 0;
     float* d_tri_pos = nullptr;
     float* d_tri_nrm = nullptr;
+    InstDev* d_tri_insts = nullptr;
+    InstDev* d_aabb_insts = nullptr;
+    Material* d_plane_mats = nullptr;
     float4* d_nodes = nullptr;
     uint32_t* d_sorted = nullptr;
     void* d_lbvh_scratch = nullptr;
@@ -197,29 +199,37 @@ int ensure_pass_buffers(gprt_ctx* c, uint32_t pixels) {
 
 int upload_static_scene(gprt_ctx* c) {
     const uint32_t n = (uint32_t)c->h_aabbs.size();
-    // primitive records from the hit-group table: record index = rayType + 2*geometryIndex + contribution
-    std::vector<PrimRecord> prims(n);
+    const uint32_t n_ai = c->have_aabb_instance ? (uint32_t)c->h_aabb_insts.size() : 0u;
+    // primitive records from the hit-group table: record index = rayType + 2*geometryIndex + the instance's
+    // contribution; one block of n records per AABB instance (instance * n + geometryIndex)
+    std::vector<PrimRecord> prims((size_t)n * (n_ai ? n_ai : 1u));
     c->type_mask = 0;
     c->max_instance_index = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        const size_t ri = (size_t)c->aabb_contrib + 2 * (size_t)i;
-        if (ri >= c->h_records.size()) return GPRT_E_INVALID_ARG;
-        const gprt_hit_group_record& rec = c->h_records[ri];
-        PrimRecord& p = prims[i];
-        std::memset(&p, 0, sizeof p);
-        p.mat = to_material(rec.material_cb);
-        p.instance_index = rec.aabb_cb.instance_index;
-        if (p.instance_index > c->max_instance_index) c->max_instance_index = p.instance_index;
-        switch (rec.shader_id[0]) {
-        case GPRT_HG_AABB_ANALYTIC: if (rec.aabb_cb.primitive_type >= GPRT_ANALYTIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = rec.aabb_cb.primitive_type; break;
-        case GPRT_HG_AABB_VOLUMETRIC: if (rec.aabb_cb.primitive_type >= GPRT_VOLUMETRIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 2; break;
-        case GPRT_HG_AABB_SDF: if (rec.aabb_cb.primitive_type >= GPRT_SDF_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 3 + rec.aabb_cb.primitive_type; break;
-        default: return GPRT_E_INVALID_ARG;
+    bool types_agree = true;
+    for (uint32_t k = 0; k < n_ai; k++) {
+        const uint32_t contrib = c->h_aabb_insts[k].hit_group_contrib_and_flags & 0xFFFFFFu;
+        for (uint32_t i = 0; i < n; i++) {
+            const size_t ri = (size_t)contrib + 2 * (size_t)i;
+            if (ri >= c->h_records.size()) return GPRT_E_INVALID_ARG;
+            const gprt_hit_group_record& rec = c->h_records[ri];
+            PrimRecord& p = prims[(size_t)k * n + i];
+            std::memset(&p, 0, sizeof p);
+            p.mat = to_material(rec.material_cb);
+            p.instance_index = rec.aabb_cb.instance_index;
+            if (p.instance_index > c->max_instance_index) c->max_instance_index = p.instance_index;
+            switch (rec.shader_id[0]) {
+            case GPRT_HG_AABB_ANALYTIC: if (rec.aabb_cb.primitive_type >= GPRT_ANALYTIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = rec.aabb_cb.primitive_type; break;
+            case GPRT_HG_AABB_VOLUMETRIC: if (rec.aabb_cb.primitive_type >= GPRT_VOLUMETRIC_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 2; break;
+            case GPRT_HG_AABB_SDF: if (rec.aabb_cb.primitive_type >= GPRT_SDF_COUNT) return GPRT_E_INVALID_ARG; p.type_id = 3 + rec.aabb_cb.primitive_type; break;
+            default: return GPRT_E_INVALID_ARG;
+            }
+            c->type_mask |= 1u << p.type_id;
+            if (p.type_id != prims[i].type_id) types_agree = false;
         }
-        c->type_mask |= 1u << p.type_id;
     }
     // triangles: positions per triangle + the normal of the vertex indices[0] names (src/Raytracing.hlsl:184)
     const uint32_t n_tris = c->have_tri_instance ? (uint32_t)(c->h_indices.size() / 3) : 0;
+    const uint32_t n_ti = n_tris ? (uint32_t)c->h_tri_insts.size() : 0u;
     std::vector<float> tri_pos(9 * (size_t)n_tris), tri_nrm(3 * (size_t)n_tris);
     for (uint32_t t = 0; t < n_tris; t++) {
         for (int k = 0; k < 3; k++) {
@@ -229,31 +239,51 @@ int upload_static_scene(gprt_ctx* c) {
         }
         for (int a = 0; a < 3; a++) tri_nrm[3 * t + a] = c->h_vertices[c->h_indices[3 * t]].normal[a];
     }
-    if (n_tris && c->tri_contrib >= c->h_records.size()) return GPRT_E_INVALID_ARG;
+    std::vector<Material> plane_mats(n_ti ? n_ti : 1u);
+    std::vector<InstDev> tri_insts(n_ti ? n_ti : 1u), aabb_insts(n_ai ? n_ai : 1u);
+    for (uint32_t k = 0; k < n_ti; k++) {
+        const uint32_t contrib = c->h_tri_insts[k].hit_group_contrib_and_flags & 0xFFFFFFu;
+        if (contrib >= c->h_records.size()) return GPRT_E_INVALID_ARG;
+        plane_mats[k] = to_material(c->h_records[contrib].material_cb);
+        invert_affine_3x4(c->h_tri_insts[k].transform, tri_insts[k].w2o);
+        std::memcpy(tri_insts[k].o2w, c->h_tri_insts[k].transform, sizeof tri_insts[k].o2w);
+    }
+    for (uint32_t k = 0; k < n_ai; k++) {
+        invert_affine_3x4(c->h_aabb_insts[k].transform, aabb_insts[k].w2o);
+        std::memcpy(aabb_insts[k].o2w, c->h_aabb_insts[k].transform, sizeof aabb_insts[k].o2w);
+    }
 
     cudaStreamSynchronize(c->stream);
     cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch);
+    cudaFree(c->d_tri_insts); cudaFree(c->d_aabb_insts); cudaFree(c->d_plane_mats);
     c->d_aabbs = nullptr; c->d_prims = nullptr; c->d_prim_types = nullptr; c->d_tri_pos = c->d_tri_nrm = nullptr; c->d_nodes = nullptr; c->d_sorted = nullptr; c->d_lbvh_scratch = nullptr;
+    c->d_tri_insts = c->d_aabb_insts = nullptr; c->d_plane_mats = nullptr;
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_aabbs, (size_t)(n ? n : 1) * 6 * sizeof(float)));
-    GPRT_CUDA(c, cudaMalloc((void**)&c->d_prims, (size_t)(n ? n : 1) * sizeof(PrimRecord)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_prims, (prims.size() + 1) * sizeof(PrimRecord)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_prim_types, (size_t)(n ? n : 1)));
     std::vector<uint8_t> types(n);
-    for (uint32_t i = 0; i < n; i++) types[i] = (uint8_t)prims[i].type_id;
+    for (uint32_t i = 0; i < n && n_ai; i++) types[i] = (uint8_t)prims[i].type_id;
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_pos, (tri_pos.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_nrm, (tri_nrm.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_nodes, (size_t)(n ? n : 1) * 4 * sizeof(float4)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_sorted, (size_t)(n ? n : 1) * sizeof(uint32_t)));
     GPRT_CUDA(c, cudaMalloc(&c->d_lbvh_scratch, lbvh_scratch_bytes(n ? n : 1)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_insts, tri_insts.size() * sizeof(InstDev)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_aabb_insts, aabb_insts.size() * sizeof(InstDev)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_plane_mats, plane_mats.size() * sizeof(Material)));
     if (n) {
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
-        GPRT_CUDA(c, cudaMemcpyAsync(c->d_prims, prims.data(), (size_t)n * sizeof(PrimRecord), cudaMemcpyHostToDevice, c->stream));
+        GPRT_CUDA(c, cudaMemcpyAsync(c->d_prims, prims.data(), prims.size() * sizeof(PrimRecord), cudaMemcpyHostToDevice, c->stream));
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_prim_types, types.data(), (size_t)n, cudaMemcpyHostToDevice, c->stream));
     }
     if (n_tris) {
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_pos, tri_pos.data(), tri_pos.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
         GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_nrm, tri_nrm.data(), tri_nrm.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     }
+    GPRT_CUDA(c, cudaMemcpyAsync(c->d_tri_insts, tri_insts.data(), tri_insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, c->stream));
+    GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabb_insts, aabb_insts.data(), aabb_insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, c->stream));
+    GPRT_CUDA(c, cudaMemcpyAsync(c->d_plane_mats, plane_mats.data(), plane_mats.size() * sizeof(Material), cudaMemcpyHostToDevice, c->stream));
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream)); // the host vectors above go out of scope
 
     SceneDev& s = c->scene;
@@ -266,13 +296,19 @@ int upload_static_scene(gprt_ctx* c) {
     s.tri_pos = c->d_tri_pos;
     s.tri_nrm = c->d_tri_nrm;
     s.n_tris = n_tris;
-    s.has_aabb_instance = c->have_aabb_instance ? 1u : 0u;
-    if (c->have_tri_instance) invert_affine_3x4(c->h_instances[0].transform, s.tri_w2o);
-    if (c->have_aabb_instance) {
-        invert_affine_3x4(c->h_instances[1].transform, s.aabb_w2o);
-        std::memcpy(s.aabb_o2w, c->h_instances[1].transform, sizeof s.aabb_o2w);
+    s.has_aabb_instance = n_ai ? 1u : 0u;
+    s.n_tri_insts = n_ti;
+    s.n_aabb_insts = n_ai;
+    s.tri_insts = c->d_tri_insts;
+    s.aabb_insts = c->d_aabb_insts;
+    s.plane_mats = c->d_plane_mats;
+    s.leaf_types_valid = types_agree ? 1u : 0u;
+    if (n_ti) std::memcpy(s.tri_w2o, tri_insts[0].w2o, sizeof s.tri_w2o);
+    if (n_ai) {
+        std::memcpy(s.aabb_w2o, aabb_insts[0].w2o, sizeof s.aabb_w2o);
+        std::memcpy(s.aabb_o2w, aabb_insts[0].o2w, sizeof s.aabb_o2w);
     }
-    if (n_tris) s.plane_mat = to_material(c->h_records[c->tri_contrib].material_cb);
+    if (n_ti) s.plane_mat = plane_mats[0];
     return GPRT_OK;
 }
 
@@ -394,7 +430,6 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     { const char* e = getenv("GPRT_SPILL_CAPACITY"); c->spill_capacity_limit = e ? (uint32_t)atoi(e) : 0u; }
     std::memset(&c->scene, 0, sizeof c->scene);
     std::memset(&c->wb, 0, sizeof c->wb);
-    std::memset(c->h_instances, 0, sizeof c->h_instances);
     if (cudaSetDevice(device_ordinal) != cudaSuccess) { delete c; return GPRT_E_NO_DEVICE; }
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
     c->own_stream = ok;
@@ -413,6 +448,7 @@ void gprt_destroy(gprt_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_pass_buffers(c);
+    cudaFree(c->d_tri_insts); cudaFree(c->d_aabb_insts); cudaFree(c->d_plane_mats);
     cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_per_frame); cudaFree(c->d_anim); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_fb); cudaFree(c->d_fb_ids);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
@@ -445,18 +481,17 @@ int gprt_set_geometry(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs, con
     if (!c || (n_aabbs && !aabbs) || (n_vertices && !vertices) || (n_indices && !indices) || (n_instances && !instances)) return GPRT_E_INVALID_ARG;
     if (n_indices % 3 != 0) return GPRT_E_INVALID_ARG;
     if (n_aabbs >= (1u << 27)) return GPRT_E_UNSUPPORTED; // leaf refs: 27 bits of primitive index + 4 bits of type
-    if (n_instances > 2) return GPRT_E_UNSUPPORTED; // the reference's TLAS: one triangle BLAS instance + one AABB BLAS instance
+    // TLAS: any number of instances of the triangle BLAS and of the AABB BLAS (the reference has one of each);
+    // candidates and hit ids are flattened as instance * count + index, 27 bits
     c->have_tri_instance = c->have_aabb_instance = false;
+    c->h_tri_insts.clear(); c->h_aabb_insts.clear();
     for (uint32_t i = 0; i < n_instances; i++) {
-        const uint32_t contrib = instances[i].hit_group_contrib_and_flags & 0xFFFFFFu;
-        if (instances[i].acceleration_structure == GPRT_BLAS_TRIANGLES) {
-            if (c->have_tri_instance) return GPRT_E_UNSUPPORTED;
-            c->h_instances[0] = instances[i]; c->have_tri_instance = n_indices >= 3; c->tri_contrib = contrib;
-        } else if (instances[i].acceleration_structure == GPRT_BLAS_AABBS) {
-            if (c->have_aabb_instance) return GPRT_E_UNSUPPORTED;
-            c->h_instances[1] = instances[i]; c->have_aabb_instance = n_aabbs > 0; c->aabb_contrib = contrib;
-        } else return GPRT_E_INVALID_ARG;
+        if (instances[i].acceleration_structure == GPRT_BLAS_TRIANGLES) { c->h_tri_insts.push_back(instances[i]); c->have_tri_instance = n_indices >= 3; }
+        else if (instances[i].acceleration_structure == GPRT_BLAS_AABBS) { c->h_aabb_insts.push_back(instances[i]); c->have_aabb_instance = n_aabbs > 0; }
+        else return GPRT_E_INVALID_ARG;
     }
+    if (c->h_tri_insts.size() > kMaxInstancesPerKind || c->h_aabb_insts.size() > kMaxInstancesPerKind) return GPRT_E_UNSUPPORTED;
+    if ((uint64_t)c->h_aabb_insts.size() * n_aabbs >= (1u << 27) || (uint64_t)c->h_tri_insts.size() * (n_indices / 3) >= (1u << 27)) return GPRT_E_UNSUPPORTED;
     c->h_aabbs.assign(aabbs, aabbs + n_aabbs);
     c->h_vertices.assign(vertices, vertices + n_vertices);
     c->h_indices.assign(indices, indices + n_indices);

@@ -77,6 +77,17 @@ __device__ __forceinline__ void add_candidate(const PassParams& pp, const WaveBu
     }
 }
 
+// A leaf the ray's slab test passed: `tagged` = primitive | type id << 27.  The tag is the type in the FIRST AABB
+// instance's hit groups; if another instance maps a primitive to another intersection shader, the record decides.
+// (MULTI = false: the reference's TLAS shape, one instance per BLAS; the kernels are compiled for both.)
+template <bool MULTI>
+__device__ __forceinline__ void add_leaf(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, uint32_t flat0,
+                                         uint32_t tagged, Pending& pend) {
+    const uint32_t flat = (MULTI ? flat0 : 0u) + (tagged & kLeafPrimMask);
+    const uint32_t type = (!MULTI || sc.leaf_types_valid) ? (tagged >> kLeafTypeShift) : sc.prims[flat].type_id;
+    add_candidate(pp, wb, ctrl, r, flat, type, pend);
+}
+
 // Walks the subtree under `root` for ray r; every box whose slab test passes on [TMin, tcur] is a candidate.
 // A grazing ray crosses hundreds of boxes (2000+ dependent node fetches at 1 M primitives), and left to one thread
 // that chain, not the throughput, sets the kernel's duration.  So a walk has a node budget (pp.spill_budget), after
@@ -91,10 +102,11 @@ __device__ __forceinline__ void add_candidate(const PassParams& pp, const WaveBu
 enum WalkMode { kWalkDepthFirst = 0, kWalkDepthFirstBudget = 1, kWalkBreadthFirst = 2 };
 constexpr uint32_t kBreadthBudgetMax = 48; // the frontier grows by at most one entry per fetch and must fit the 64-entry ring
 
-template <int MODE>
+template <int MODE, bool MULTI>
 __device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, V3 oo, V3 inv_d,
-                                              float tcur, int32_t root, uint2* spill_q, uint32_t* spill_count, Pending& pend) {
+                                              float tcur, int32_t root, uint32_t inst, uint2* spill_q, uint32_t* spill_count, Pending& pend) {
     const float tmin = 0.0f;
+    const uint32_t flat0 = MULTI ? inst * sc.n_prims : 0u; // candidates are numbered instance * n_prims + primitive
     int32_t ring[64];
     uint32_t head = 0, tail = 0; // live entries: ring[head .. tail) mod 64
     ring[tail++] = root;
@@ -107,7 +119,7 @@ __device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassPara
             const uint32_t n = tail - head;
             const uint32_t at = atomicAdd(spill_count, n);
             if (at + n <= wb.spill_capacity) {
-                for (uint32_t i = 0; i < n; i++) spill_q[at + i] = make_uint2(r, (uint32_t)ring[(head + i) & 63u]);
+                for (uint32_t i = 0; i < n; i++) spill_q[at + i] = make_uint2(MULTI ? (r | (inst << kSpillRayBits)) : r, (uint32_t)ring[(head + i) & 63u]);
                 break;
             }
             // queue full: void the reserved slots that exist and finish the walk here
@@ -123,11 +135,11 @@ __device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassPara
         const float lo1[3] = {b.z, b.w, c.x}, hi1[3] = {c.y, c.z, c.w};
         const int32_t ref0 = __float_as_int(e.x), ref1 = __float_as_int(e.y);
         if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
-            if (ref0 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref0 & kLeafPrimMask, (uint32_t)~ref0 >> kLeafTypeShift, pend);
+            if (ref0 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref0, pend);
             else if (tail - head < 64u) ring[tail++ & 63u] = ref0;
         }
         if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
-            if (ref1 < 0) add_candidate(pp, wb, ctrl, r, (uint32_t)~ref1 & kLeafPrimMask, (uint32_t)~ref1 >> kLeafTypeShift, pend);
+            if (ref1 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref1, pend);
             else if (tail - head < 64u) ring[tail++ & 63u] = ref1;
         }
     }
@@ -135,7 +147,7 @@ __device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassPara
 }
 
 // One ray: plane, then the AABB tree.  Writes hitkey / ray_tcur, collects candidates in `pend`.
-template <bool PRIMARY>
+template <bool PRIMARY, bool MULTI>
 __device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, uint32_t r,
                                                  Pending& pend) {
     V3 o, d;
@@ -156,9 +168,12 @@ __device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassP
     float tcur = kRayTMax;
     unsigned long long key = kKeyMiss;
 
-    // (i) triangle instance
-    if (sc.n_tris) {
-        const V3 oo = xform_point_3x4(sc.tri_w2o, o), dd = xform_vector_3x4(sc.tri_w2o, d);
+    // (i) triangle instances, TLAS order (the reference has one: the ground quad)
+    const uint32_t n_ti = MULTI ? sc.n_tri_insts : min(sc.n_tri_insts, 1u);
+    for (uint32_t ti = 0; ti < n_ti; ti++) {
+        const float* w2o = (MULTI && ti) ? sc.tri_insts[ti].w2o : sc.tri_w2o;
+        const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
+        bool stop = false;
         for (uint32_t tri = 0; tri < sc.n_tris; tri++) {
             const float* p = sc.tri_pos + 9 * tri;
             const V3 v0 = v3(p[0], p[1], p[2]);
@@ -176,27 +191,34 @@ __device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassP
             const float t = dot(e2, qvec) * inv_det;
             if (t > tmin && t < tcur) {
                 tcur = t;
-                key = pack_key(t, kCodePlane | tri);
-                if (shadow) break;
+                key = pack_key(t, kCodePlane | ((MULTI ? ti * sc.n_tris : 0u) + tri));
+                if (shadow) { stop = true; break; }
             }
         }
+        if (stop) break;
     }
     wb.hitkey[r] = key;
     wb.ray_tcur[r] = tcur;
     if (shadow && key != kKeyMiss) return 0u; // ACCEPT_FIRST_HIT_AND_END_SEARCH
     if (!sc.has_aabb_instance || sc.n_prims == 0) return 0u;
 
-    // (ii) procedural AABBs
-    const V3 oo = xform_point_3x4(sc.aabb_w2o, o), dd = xform_vector_3x4(sc.aabb_w2o, d);
-    const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
-    if (pp.brute_force || sc.root_ref < 0) {
-        for (uint32_t i = 0; i < sc.n_prims; i++) {
-            const float* b = sc.aabbs + 6 * i;
-            if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) add_candidate(pp, wb, ctrl, r, i, sc.prims[i].type_id, pend);
+    // (ii) procedural AABBs, one walk of the (shared) BLAS per TLAS instance in that instance's object space
+    uint32_t visits = 0;
+    const uint32_t n_ai = MULTI ? sc.n_aabb_insts : 1u;
+    for (uint32_t k = 0; k < n_ai; k++) {
+        const float* w2o = (MULTI && k) ? sc.aabb_insts[k].w2o : sc.aabb_w2o;
+        const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
+        const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
+        if (pp.brute_force || sc.root_ref < 0) {
+            for (uint32_t i = 0; i < sc.n_prims; i++) {
+                const float* b = sc.aabbs + 6 * i;
+                if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) add_candidate(pp, wb, ctrl, r, (MULTI ? k * sc.n_prims : 0u) + i, sc.prims[(MULTI ? k * sc.n_prims : 0u) + i].type_id, pend);
+            }
+        } else {
+            visits += walk_tree<kWalkDepthFirstBudget, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, sc.root_ref, k, wb.spill[0], &ctrl->spill_count[0], pend);
         }
-        return 0u;
     }
-    return walk_tree<kWalkDepthFirstBudget>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, sc.root_ref, wb.spill[0], &ctrl->spill_count[0], pend);
+    return visits;
 }
 
 // Convergent append of a warp's pending candidates (all 32 lanes call this).
@@ -238,7 +260,7 @@ struct VisitStats {
     }
 };
 
-template <bool PRIMARY>
+template <bool PRIMARY, bool MULTI>
 __global__ void __launch_bounds__(kBlock, 6) k_traverse(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                         const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
@@ -254,7 +276,7 @@ __global__ void __launch_bounds__(kBlock, 6) k_traverse(const __grid_constant__ 
 #pragma unroll
         for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
         uint32_t visits = 0;
-        if (r < n_rays) visits = traverse_ray<PRIMARY>(sc, pp, wb, ctrl, pq, r, pend);
+        if (r < n_rays) visits = traverse_ray<PRIMARY, MULTI>(sc, pp, wb, ctrl, pq, r, pend);
         flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
         stats.add(visits);
     };
@@ -280,6 +302,7 @@ __global__ void __launch_bounds__(kBlock, 6) k_traverse(const __grid_constant__ 
 // Spill round `round` (1..kSpillRounds): walks the (ray, subtree) entries the previous round handed over, one per
 // thread, breadth first under the node budget, except the last round, which finishes whatever is left.  Entries are short by construction, so a fixed
 // stride is enough here.
+template <bool MULTI>
 __global__ void __launch_bounds__(kBlock, 6) k_traverse_spill(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, int round) {
     __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
@@ -300,13 +323,15 @@ __global__ void __launch_bounds__(kBlock, 6) k_traverse_spill(const __grid_const
         if (i < n_in) {
             const uint2 e = in[i];
             if (e.x != 0xFFFFFFFFu) {
-                r = e.x;
+                r = MULTI ? (e.x & ((1u << kSpillRayBits) - 1u)) : e.x;
+                const uint32_t inst = MULTI ? (e.x >> kSpillRayBits) : 0u;
+                const float* w2o = (MULTI && inst) ? sc.aabb_insts[inst].w2o : sc.aabb_w2o;
                 const V3 o = ld3(wb.ray_o[pq][r]), d = ld3(wb.ray_d[pq][r]);
-                const V3 oo = xform_point_3x4(sc.aabb_w2o, o), dd = xform_vector_3x4(sc.aabb_w2o, d);
+                const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
                 const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
                 const float tcur = wb.ray_tcur[r];
-                if (last) visits = walk_tree<kWalkDepthFirst>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, nullptr, nullptr, pend);
-                else visits = walk_tree<kWalkBreadthFirst>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, out, &ctrl->spill_count[round], pend);
+                if (last) visits = walk_tree<kWalkDepthFirst, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, inst, nullptr, nullptr, pend);
+                else visits = walk_tree<kWalkBreadthFirst, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, inst, out, &ctrl->spill_count[round], pend);
             }
         }
         flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
@@ -320,6 +345,18 @@ __global__ void __launch_bounds__(kBlock, 6) k_traverse_spill(const __grid_const
 // (MyIntersectionShader_* + GetRayInAABBPrimitiveLocalSpace, src/Raytracing.hlsl:277-341).
 // Persistent blocks pull chunks of the queue; its length is only known on the device.
 // ---------------------------------------------------------------------------------------------
+// The TLAS instance a flattened candidate / hit id belongs to: its world <-> object transforms.
+struct InstXform { const float* w2o; const float* o2w; };
+__device__ __forceinline__ InstXform inst_xform(const SceneDev& sc, uint32_t flat) {
+    InstXform x;
+    x.w2o = sc.aabb_w2o; x.o2w = sc.aabb_o2w;
+    if (sc.n_aabb_insts > 1u) {
+        const uint32_t k = flat / sc.n_prims;
+        if (k) { x.w2o = sc.aabb_insts[k].w2o; x.o2w = sc.aabb_insts[k].o2w; }
+    }
+    return x;
+}
+
 template <int TYPE, int NB>
 __device__ __forceinline__ bool run_test(const LocalRay& lr, const Material& mat, const PassParams& pp, float& thit, V3& n, uint32_t& work) {
     if (TYPE == 0) { work++; return ray_unit_box(lr, thit, n); }
@@ -353,7 +390,8 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
             const float4 ro = wb.ray_o[pq][r];
             const PrimRecord pr = sc.prims[prim];
             const float* pf = sc.per_frame + 32 * (size_t)pr.instance_index;
-            const V3 oo = xform_point_3x4(sc.aabb_w2o, ld3(ro)), dd = xform_vector_3x4(sc.aabb_w2o, ld3(rd));
+            const InstXform ix = inst_xform(sc, prim);
+            const V3 oo = xform_point_3x4(ix.w2o, ld3(ro)), dd = xform_vector_3x4(ix.w2o, ld3(rd));
             LocalRay lr;
             lr.o = mul_point_rowvec(oo, pf + 16);
             lr.d = mul_vector_rowvec(dd, pf + 16);
@@ -371,7 +409,7 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
             if (hit && thit >= lr.tmin && thit <= lr.tcur) {
                 // attr.normal = mul(n, (float3x3)local_to_blas); normalize(mul((float3x3)ObjectToWorld3x4(), attr.normal))
                 const V3 nb = mul_vector_rowvec(n, pf);
-                const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
+                const V3 nw = normalize(xform_vector_3x4(ix.o2w, nb));
                 atomicMin(&wb.hitkey[r], pack_key(thit, prim));
                 res = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
             }
@@ -440,9 +478,10 @@ __global__ void __launch_bounds__(kBlock) k_shade_spawn(const __grid_constant__ 
                     V3 n;
                     float refl;
                     if (code & kCodePlane) {
-                        const float* tn = sc.tri_nrm + 3 * (code & ~kCodePlane);
-                        n = v3(tn[0], tn[1], tn[2]);
-                        refl = sc.plane_mat.reflectance_coefficient;
+                        const uint32_t ft = code & ~kCodePlane; // triangle instance * n_tris + triangle
+                        const float* tn = sc.tri_nrm + 3 * (sc.n_tri_insts > 1u ? ft % sc.n_tris : ft);
+                        n = v3(tn[0], tn[1], tn[2]); // the vertex normal as it is: the shader applies no object-to-world (src/Raytracing.hlsl:184)
+                        refl = (sc.n_tri_insts > 1u ? sc.plane_mats[ft / sc.n_tris] : sc.plane_mat).reflectance_coefficient;
                     } else {
                         n = ld3(wb.hit_n[r]);
                         refl = sc.prims[code].mat.reflectance_coefficient;
@@ -512,7 +551,7 @@ __global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ 
             if (code == kCodeMiss) { color = background_color(); continue; } // MyMissShader
             const float4 ot = wb.lvl_o_t[li], dd = wb.lvl_d[li], nn = wb.lvl_n[li];
             const bool is_tri = (code & kCodePlane) != 0u;
-            const Material mat = is_tri ? sc.plane_mat : sc.prims[code].mat;
+            const Material mat = is_tri ? (sc.n_tri_insts > 1u ? sc.plane_mats[(code & ~kCodePlane) / sc.n_tris] : sc.plane_mat) : sc.prims[code].mat;
             const bool in_shadow = ((uint32_t)level < pp.max_depth) ? (wb.lvl_shadow[li] != 0) : false;
             color = closest_hit_color(pp.fc, ld3(ot), ld3(dd), ot.w, ld3(nn), mat, in_shadow, color, is_tri, px, py);
         }
@@ -563,16 +602,21 @@ int resident_blocks(const void* kernel) {
     return n;
 }
 
-int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
-    cudaStream_t s = (cudaStream_t)stream;
+template <bool MULTI>
+int launch_traverse_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
     const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
-    static const int per_sm_primary = resident_blocks((const void*)k_traverse<true>), per_sm_secondary = resident_blocks((const void*)k_traverse<false>);
-    if (wave == 1) k_traverse<true><<<grid_for(upper, per_sm_primary), kBlock, 0, s>>>(sc, pp, wb, wave);
-    else k_traverse<false><<<grid_for(upper, per_sm_secondary), kBlock, 0, s>>>(sc, pp, wb, wave);
+    static const int per_sm_primary = resident_blocks((const void*)k_traverse<true, MULTI>), per_sm_secondary = resident_blocks((const void*)k_traverse<false, MULTI>);
+    if (wave == 1) k_traverse<true, MULTI><<<grid_for(upper, per_sm_primary), kBlock, 0, s>>>(sc, pp, wb, wave);
+    else k_traverse<false, MULTI><<<grid_for(upper, per_sm_secondary), kBlock, 0, s>>>(sc, pp, wb, wave);
     if (!pp.spill_budget) return 1;
-    static const int per_sm_spill = resident_blocks((const void*)k_traverse_spill);
-    for (int round = 1; round <= kSpillRounds; round++) k_traverse_spill<<<sm_count() * per_sm_spill, kBlock, 0, s>>>(sc, pp, wb, wave, round);
+    static const int per_sm_spill = resident_blocks((const void*)k_traverse_spill<MULTI>);
+    for (int round = 1; round <= kSpillRounds; round++) k_traverse_spill<MULTI><<<sm_count() * per_sm_spill, kBlock, 0, s>>>(sc, pp, wb, wave, round);
     return 1 + kSpillRounds;
+}
+int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {
+    // the reference's TLAS (one instance per BLAS) runs the kernels compiled without the instance loops
+    if (sc.n_tri_insts > 1u || sc.n_aabb_insts > 1u) return launch_traverse_t<true>(sc, pp, wb, wave, (cudaStream_t)stream);
+    return launch_traverse_t<false>(sc, pp, wb, wave, (cudaStream_t)stream);
 }
 
 // GPRT_ISECT_VARIANT=-1 (profiling aid): with GPRT_PER_TYPE_LAUNCHES=1, run the one-candidate-per-thread kernels, which

@@ -46,7 +46,8 @@ template <int RMIN> __device__ __forceinline__ bool refill_now(bool active) {
 }
 
 struct CandState {
-    uint32_t c, r, prim;
+    uint32_t c, r, prim; // prim: flattened instance * n_prims + primitive
+    const float* o2w;    // ObjectToWorld3x4() of the candidate's TLAS instance
     const float* pf; // per-frame transforms of the primitive: local->BLAS (16 floats), BLAS->local (16 floats)
     LocalRay lr;
     float step_scale;
@@ -68,7 +69,9 @@ __device__ __forceinline__ bool fetch_candidate(const SceneDev& sc, const WaveBu
     const PrimRecord* pr = sc.prims + s.prim;
     s.step_scale = pr->mat.step_scale;
     s.pf = sc.per_frame + 32 * (size_t)pr->instance_index;
-    const V3 oo = xform_point_3x4(sc.aabb_w2o, ld3(ro)), dd = xform_vector_3x4(sc.aabb_w2o, ld3(rd));
+    const InstXform ix = inst_xform(sc, s.prim);
+    s.o2w = ix.o2w;
+    const V3 oo = xform_point_3x4(ix.w2o, ld3(ro)), dd = xform_vector_3x4(ix.w2o, ld3(rd));
     s.lr.o = mul_point_rowvec(oo, s.pf + 16);
     s.lr.d = mul_vector_rowvec(dd, s.pf + 16);
     s.lr.tmin = 0.0f;
@@ -81,7 +84,7 @@ template <int TYPE>
 __device__ __forceinline__ void publish_hit(const SceneDev& sc, const WaveBuffers& wb, const CandState& s, float thit, V3 n_local) {
     if (thit >= s.lr.tmin && thit <= s.lr.tcur) {
         const V3 nb = mul_vector_rowvec(n_local, s.pf);
-        const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
+        const V3 nw = normalize(xform_vector_3x4(s.o2w, nb));
         atomicMin(&wb.hitkey[s.r], pack_key(thit, s.prim));
         wb.cand_res[TYPE][s.c] = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
     } else {

@@ -77,7 +77,8 @@ __device__ __forceinline__ bool fetch_lane(const SceneDev& sc, const WaveBuffers
     const PrimRecord* pr = sc.prims + cand.y;
     m.scale = pr->mat.step_scale;
     const float* pf = sc.per_frame + 32 * (size_t)pr->instance_index;
-    const V3 oo = xform_point_3x4(sc.aabb_w2o, ld3(ro)), dd = xform_vector_3x4(sc.aabb_w2o, ld3(rd));
+    const InstXform ix = inst_xform(sc, cand.y);
+    const V3 oo = xform_point_3x4(ix.w2o, ld3(ro)), dd = xform_vector_3x4(ix.w2o, ld3(rd));
     m.o = mul_point_rowvec(oo, pf + 16);
     m.d = mul_vector_rowvec(dd, pf + 16);
     m.tcur = wb.ray_tcur[m.r];
@@ -94,7 +95,7 @@ __device__ __forceinline__ void publish_lane_hit(const SceneDev& sc, const WaveB
         const uint32_t prim = wb.cand[type][m.c].y;
         const float* pf = sc.per_frame + 32 * (size_t)sc.prims[prim].instance_index;
         const V3 nb = mul_vector_rowvec(n_local, pf);
-        const V3 nw = normalize(xform_vector_3x4(sc.aabb_o2w, nb));
+        const V3 nw = normalize(xform_vector_3x4(inst_xform(sc, prim).o2w, nb));
         atomicMin(&wb.hitkey[m.r], pack_key(thit, prim));
         wb.cand_res[type][m.c] = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
     } else {

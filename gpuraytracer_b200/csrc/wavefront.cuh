@@ -43,6 +43,14 @@ struct PrimRecord { // per geometry index; 48 bytes
     uint32_t _pad;
 };
 
+// One TLAS instance (two-level instancing): the extra instances of a BLAS beyond the first of its kind.
+struct InstDev {
+    float w2o[12]; // world -> BLAS object space (3x4), inverted on the host in double
+    float o2w[12]; // ObjectToWorld3x4()
+};
+constexpr uint32_t kMaxInstancesPerKind = 256; // 8 bits of a spill entry carry the AABB instance
+constexpr uint32_t kSpillRayBits = 23;         // ray slots per pass < 2^23 (gprt_api.cu: kDefaultPassPixels = 2^22)
+
 struct SceneDev {
     const float4* bvh_nodes; // 4 x float4 per internal node: child0 min|max, child1 min|max, refs
     int32_t root_ref;        // >= 0 internal node, < 0 leaf (~primitive), INT32_MIN: no primitives
@@ -58,6 +66,14 @@ struct SceneDev {
     float aabb_w2o[12];      // world -> AABB BLAS object space
     float aabb_o2w[12];      // ObjectToWorld3x4() of the AABB instance
     Material plane_mat;
+    // two-level instancing: n_*_insts TLAS instances of each BLAS.  Instance 0 of each kind is the
+    // set of fields above; candidates, hit codes and `prims` are flattened as instance * n_prims + primitive
+    // (triangles: instance * n_tris + triangle), so everything downstream of the traversal indexes one table.
+    uint32_t n_tri_insts, n_aabb_insts;
+    const InstDev* tri_insts;    // [n_tri_insts]
+    const InstDev* aabb_insts;   // [n_aabb_insts]
+    const Material* plane_mats;  // [n_tri_insts]: the triangle hit group of each instance's contribution
+    uint32_t leaf_types_valid;   // the type tag in the leaf refs holds for every AABB instance
 };
 
 constexpr int kSpillRounds = 3; // traversal hand-over rounds after the main walk (the last one has no node budget)

@@ -168,7 +168,7 @@ int Renderer::create_device_dependent_resources() {
 int Renderer::build_geometry() {
     return gprt_set_geometry(m_ctx, m_scene.aabbs.data(), (uint32_t)m_scene.aabbs.size(), m_scene.vertices.data(),
                              (uint32_t)m_scene.vertices.size(), m_scene.indices.data(), (uint32_t)m_scene.indices.size(),
-                             m_scene.instances, 2);
+                             m_scene.instances.data(), (uint32_t)m_scene.instances.size());
 }
 
 int Renderer::build_shader_tables() {
@@ -311,7 +311,7 @@ int gprt_renderer_scene(gprt_renderer* r, gprt_scene_view* out) {
     out->hit_groups = s.hit_groups.data(); out->n_hit_groups = (uint32_t)s.hit_groups.size();
     out->vertices = s.vertices.data(); out->n_vertices = (uint32_t)s.vertices.size();
     out->indices = s.indices.data(); out->n_indices = (uint32_t)s.indices.size();
-    out->instances = s.instances; out->n_instances = 2;
+    out->instances = s.instances.data(); out->n_instances = (uint32_t)s.instances.size();
     return GPRT_OK;
 }
 

@@ -201,7 +201,8 @@ void build_geometry_and_tables(SceneState& s) {
     }
 
     // build_bottom_level_as_instance_descs, src/Renderer.cpp:732-786
-    std::memset(s.instances, 0, sizeof s.instances);
+    s.instances.assign(2, gprt_instance_desc());
+    std::memset(s.instances.data(), 0, 2 * sizeof(gprt_instance_desc));
     {
         gprt_instance_desc& d = s.instances[0];
         const Mat4 m = mat_mul(mat_scaling(s.plane_extent[0], s.plane_extent[1], s.plane_extent[2]),
@@ -220,7 +221,8 @@ void build_geometry_and_tables(SceneState& s) {
     }
 
     // build_shader_tables (hit-group table), src/Renderer.cpp:936-984
-    s.hit_groups.assign(2 + 2 * s.primitives.size(), gprt_hit_group_record());
+    const size_t n = s.primitives.size();
+    s.hit_groups.assign(2 + 2 * n, gprt_hit_group_record());
     std::memset(s.hit_groups.data(), 0, s.hit_groups.size() * sizeof(gprt_hit_group_record));
     for (uint32_t r = 0; r < 2; r++) {
         gprt_hit_group_record& rec = s.hit_groups[r];
@@ -228,7 +230,7 @@ void build_geometry_and_tables(SceneState& s) {
         rec.shader_id[1] = r;
         rec.material_cb = s.plane_material;
     }
-    for (size_t i = 0; i < s.primitives.size(); i++) {
+    for (size_t i = 0; i < n; i++) {
         for (uint32_t r = 0; r < 2; r++) {
             gprt_hit_group_record& rec = s.hit_groups[2 + 2 * i + r];
             rec.shader_id[0] = s.primitives[i].hit_group_kind;
@@ -238,6 +240,50 @@ void build_geometry_and_tables(SceneState& s) {
             rec.aabb_cb.primitive_type = s.primitives[i].primitive_type;
         }
     }
+    if (!s.extra_instances) return;
+
+    // Two-level instancing (not in the reference, which has one instance per BLAS): two more instances of the AABB
+    // BLAS -- one scaled and rotated that shares the first one's hit groups, one whose
+    // InstanceContributionToHitGroupIndex selects a second block of records (other materials, and the two
+    // 2x2x2 SDF primitives MiniSpheres / IntersectedRoundCube swapped, so a primitive's intersection shader
+    // depends on the instance) -- and a second instance of the quad as a raised mirror panel with its own record.
+    const uint32_t block_b = (uint32_t)(2 + 2 * n), panel = (uint32_t)(2 + 4 * n);
+    s.hit_groups.resize(2 + 4 * n + 2);
+    for (size_t i = 0; i < n; i++) {
+        for (uint32_t r = 0; r < 2; r++) {
+            gprt_hit_group_record rec = s.hit_groups[2 + 2 * i + r];
+            const float a0 = rec.material_cb.albedo[0];
+            rec.material_cb.albedo[0] = rec.material_cb.albedo[2];
+            rec.material_cb.albedo[2] = a0;
+            rec.material_cb.reflectance_coefficient = rec.material_cb.reflectance_coefficient > 0.5f ? 0.0f : 0.3f;
+            if (rec.shader_id[0] == GPRT_HG_AABB_SDF && rec.aabb_cb.primitive_type == GPRT_SDF_MINI_SPHERES) rec.aabb_cb.primitive_type = GPRT_SDF_INTERSECTED_ROUND_CUBE;
+            else if (rec.shader_id[0] == GPRT_HG_AABB_SDF && rec.aabb_cb.primitive_type == GPRT_SDF_INTERSECTED_ROUND_CUBE) rec.aabb_cb.primitive_type = GPRT_SDF_MINI_SPHERES;
+            s.hit_groups[block_b + 2 * i + r] = rec;
+        }
+    }
+    const float red[4] = {1.0f, 0.45f, 0.4f, 1.0f};
+    for (uint32_t r = 0; r < 2; r++) {
+        gprt_hit_group_record rec = s.hit_groups[r];
+        rec.material_cb = make_material(red, 0.6f, 0.9f, 0.7f, 50, 1);
+        s.hit_groups[panel + r] = rec;
+    }
+    const float* tr = s.aabb_instance_translate;
+    gprt_instance_desc d;
+    std::memset(&d, 0, sizeof d);
+    d.instance_id_and_mask = (1u << 24) | 1u;
+    d.hit_group_contrib_and_flags = 2;
+    d.acceleration_structure = GPRT_BLAS_AABBS;
+    mat_store_3x4(mat_mul(mat_mul(mat_scaling(0.7, 0.7, 0.7), mat_rotation_y(0.6)), mat_translation(tr[0] + 17.0, tr[1] + 0.0, tr[2] + 5.0)), d.transform);
+    s.instances.push_back(d);
+    d.instance_id_and_mask = (1u << 24) | 2u;
+    d.hit_group_contrib_and_flags = block_b;
+    mat_store_3x4(mat_mul(mat_rotation_y(-0.9), mat_translation(tr[0] - 14.0, tr[1] + 0.0, tr[2] + 9.0)), d.transform);
+    s.instances.push_back(d);
+    d.instance_id_and_mask = (1u << 24) | 3u;
+    d.hit_group_contrib_and_flags = panel;
+    d.acceleration_structure = GPRT_BLAS_TRIANGLES;
+    mat_store_3x4(mat_mul(mat_scaling(8.0, 1.0, 8.0), mat_translation(-4.0, 4.0, 14.0)), d.transform);
+    s.instances.push_back(d);
 }
 
 bool build_scene(SceneState& s, int scene_id, uint32_t width, uint32_t height, uint32_t grid_n) {
@@ -260,6 +306,12 @@ bool build_scene(SceneState& s, int scene_id, uint32_t width, uint32_t height, u
     case kConfig2:
         s.width = width ? width : 1920; s.height = height ? height : 1080;
         reference_primitives(s);
+        break;
+    case kInstanced:
+        s.width = width ? width : 1280; s.height = height ? height : 720;
+        reference_primitives(s);
+        s.extra_instances = true;
+        eye[1] = 9.0; eye[2] = -36.0;
         break;
     case kConfig1: {
         // one analytic sphere-cluster AABB + the ground quad, primary + shadow rays only:

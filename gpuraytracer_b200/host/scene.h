@@ -46,14 +46,16 @@ struct SceneState {
     std::vector<gprt_hit_group_record> hit_groups;
     std::vector<gprt_vertex> vertices;
     std::vector<uint16_t> indices;
-    gprt_instance_desc instances[2];
+    std::vector<gprt_instance_desc> instances; // the TLAS: [0] the ground quad, [1] the AABB BLAS (src/Renderer.cpp:732-786); kInstanced adds more
+    bool extra_instances = false;              // kInstanced: three AABB instances + a second triangle instance
 
     float animate_geometry_time = 0.0f;
 };
 
 // Scene ids: 0 = the reference scene at the caller's size (src/Renderer.cpp);
 // 1..5 = the five BASELINE.json configs made concrete.
-enum SceneId { kSceneReference = 0, kConfig1 = 1, kConfig2 = 2, kConfig3 = 3, kConfig4 = 4, kConfig5 = 5, kConfig3Long = 6 };
+// 7 = the reference primitives under a TLAS with several instances of each BLAS (two-level instancing).
+enum SceneId { kSceneReference = 0, kConfig1 = 1, kConfig2 = 2, kConfig3 = 3, kConfig4 = 4, kConfig5 = 5, kConfig3Long = 6, kInstanced = 7 };
 
 // width/height == 0 selects the config's own resolution.  grid_n overrides the grid edge of
 // config 5 (0 = 1000) so tests can use a small instance grid.

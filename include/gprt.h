@@ -206,8 +206,11 @@ void gprt_destroy(gprt_ctx* ctx);
 /* Replaces Renderer::build_geometry + the geometry/instance descs of
  * build_geometry_descs_for_bottom_level_as / build_bottom_level_as_instance_descs
  * (src/Renderer.cpp:478-565, 567-612, 732-786).  Host arrays are copied during the call.
- * The reference's TLAS is exactly {triangle BLAS instance, AABB BLAS instance}; that is what is
- * accepted: instances[i].acceleration_structure selects GPRT_BLAS_TRIANGLES or GPRT_BLAS_AABBS. */
+ * instances[i].acceleration_structure selects GPRT_BLAS_TRIANGLES or GPRT_BLAS_AABBS.  The
+ * reference's TLAS is exactly {triangle BLAS instance, AABB BLAS instance}; any number of instances
+ * of either BLAS (up to 256 of a kind) is accepted, each with its own 3x4 transform and
+ * InstanceContributionToHitGroupIndex (two-level instancing).  Instances of a kind are numbered in
+ * array order; instance_count * primitive_count must stay below 2^27. */
 int gprt_set_geometry(gprt_ctx* ctx,
                       const gprt_aabb* aabbs, uint32_t n_aabbs,
                       const gprt_vertex* vertices, uint32_t n_vertices,
@@ -289,8 +292,8 @@ int gprt_dispatch_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
 void* gprt_get_stream(gprt_ctx* ctx);
 
 #define GPRT_HIT_MISS     0xFFFFFFFFu
-#define GPRT_HIT_TRIANGLE 0x00000000u /* | PrimitiveIndex()  (instance 0)               */
-#define GPRT_HIT_AABB     0x10000000u /* | GeometryIndex     (instance 1)               */
+#define GPRT_HIT_TRIANGLE 0x00000000u /* | triangle instance ordinal * triangle count + PrimitiveIndex() */
+#define GPRT_HIT_AABB     0x10000000u /* | AABB instance ordinal * AABB count + GeometryIndex            */
 
 int gprt_sync(gprt_ctx* ctx);
 int gprt_get_counters(gprt_ctx* ctx, gprt_counters* out); /* of the last dispatch; syncs */

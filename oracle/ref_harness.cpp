@@ -21,6 +21,11 @@
 //   (iii) the smallest reported t wins, ties go to the lowest geometry index, and a procedural
 //         hit at exactly the triangle's t replaces it (ReportHit's interval is closed);
 //   (iv)  RAY_FLAG_ACCEPT_FIRST_HIT_AND_END_SEARCH stops at the first reported hit.
+// With several TLAS instances of a BLAS (two-level instancing) the same order runs
+// over all instances of a kind in TLAS order: (i) over every triangle instance (the closest
+// t wins, the first instance on a tie), (ii) over every AABB instance with the ray taken into that
+// instance's object space and the hit-group record found through ITS
+// InstanceContributionToHitGroupIndex; ties go to the lowest (instance, geometry index).
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load the library built from this file.  The product (libgprt.so) never does.
@@ -146,8 +151,8 @@ struct Scene {
     std::vector<gprt_vertex> vertices;
     std::vector<uint16_t> indices; // padded by one dword so Load2 never reads past the end
     uint32_t n_indices = 0;
-    float3x4 tri_o2w, tri_w2o, aabb_o2w, aabb_w2o;
-    uint tri_contrib = 0, aabb_contrib = 2;
+    struct Inst { float3x4 o2w, w2o; uint contrib = 0; };
+    std::vector<Inst> tri_insts, aabb_insts; // TLAS instances per BLAS kind, in TLAS order
     bool has_tri = false, has_aabb = false;
     std::vector<gprt_prim_per_frame> per_frame;
     std::vector<HostBvhNode> bvh;
@@ -248,6 +253,7 @@ struct CommittedHit {
     int kind = 0; // 0 miss, 1 triangle, 2 procedural
     float t = 0;
     uint index = 0; // triangle index or geometry index
+    uint inst = 0;  // ordinal of the TLAS instance among those of its kind
     ProceduralPrimitiveAttributes attr;
     float2 bary;
 };
@@ -261,8 +267,8 @@ static void bind_local_root(const gprt_hit_group_record& rec) {
     std::memcpy(static_cast<PrimitiveInstanceConstantBuffer*>(&l_aabbCB), &rec.aabb_cb, sizeof(PrimitiveInstanceConstantBuffer));
 }
 
-static void run_candidate(uint geom, uint hit_group_offset, uint stride, bool first_hit, CommittedHit& best, bool& done) {
-    const gprt_hit_group_record& rec = hit_record(hit_group_offset + stride * geom + g_sc.aabb_contrib);
+static void run_candidate(uint inst, uint geom, uint hit_group_offset, uint stride, bool first_hit, CommittedHit& best, bool& done) {
+    const gprt_hit_group_record& rec = hit_record(hit_group_offset + stride * geom + g_sc.aabb_insts[inst].contrib);
     bind_local_root(rec);
     tl_reported.any = false;
     switch (rec.shader_id[0]) {
@@ -272,8 +278,8 @@ static void run_candidate(uint geom, uint hit_group_offset, uint stride, bool fi
     default: std::fprintf(stderr, "oracle: bad hit group kind %u\n", rec.shader_id[0]); std::abort();
     }
     if (tl_reported.any) {
-        if (best.kind != 2 || tl_reported.t < best.t || (tl_reported.t == best.t && geom < best.index)) {
-            best.kind = 2; best.t = tl_reported.t; best.index = geom; best.attr = tl_reported.attr;
+        if (best.kind != 2 || tl_reported.t < best.t || (tl_reported.t == best.t && (inst < best.inst || (inst == best.inst && geom < best.index)))) {
+            best.kind = 2; best.t = tl_reported.t; best.index = geom; best.inst = inst; best.attr = tl_reported.attr;
         }
         if (first_hit) done = true;
     }
@@ -314,11 +320,11 @@ static void trace_core(uint flags, uint hit_group_offset, uint stride, const Ray
     CommittedHit tri_hit, proc_hit;
     bool done = false;
 
-    // (i) triangle instance
-    if (g_sc.has_tri) {
-        const float3 o = xform_point(g_sc.tri_w2o, ray.Origin);
-        const float3 d = xform_vector(g_sc.tri_w2o, ray.Direction);
-        float tbest = ray.TMax;
+    // (i) triangle instances
+    float tbest = ray.TMax;
+    for (uint ti = 0; g_sc.has_tri && ti < (uint)g_sc.tri_insts.size() && !done; ti++) {
+        const float3 o = xform_point(g_sc.tri_insts[ti].w2o, ray.Origin);
+        const float3 d = xform_vector(g_sc.tri_insts[ti].w2o, ray.Direction);
         for (uint tri = 0; tri * 3 + 2 < g_sc.n_indices && !done; tri++) {
             const gprt_vertex& a = g_sc.vertices[g_sc.indices[tri * 3 + 0]];
             const gprt_vertex& b = g_sc.vertices[g_sc.indices[tri * 3 + 1]];
@@ -342,26 +348,26 @@ static void trace_core(uint flags, uint hit_group_offset, uint stride, const Ray
             const float t = dot(e2, qvec) * inv_det;
             if (t > ray.TMin && t < tbest) {
                 tbest = t;
-                tri_hit.kind = 1; tri_hit.t = t; tri_hit.index = tri; tri_hit.bary = float2(u, v);
+                tri_hit.kind = 1; tri_hit.t = t; tri_hit.index = tri; tri_hit.inst = ti; tri_hit.bary = float2(u, v);
                 if (first_hit) done = true;
             }
         }
     }
 
-    // (ii) procedural AABB instance, all candidates see TCurrent = min(TMax, t_triangle)
-    if (g_sc.has_aabb && !done) {
+    // (ii) procedural AABB instances, all candidates see TCurrent = min(TMax, t_triangle)
+    for (uint k = 0; g_sc.has_aabb && k < (uint)g_sc.aabb_insts.size() && !done; k++) {
         const float tcur = tri_hit.kind ? tri_hit.t : ray.TMax;
         tl_ray.tcurrent = tcur;
-        tl_ray.object_origin = xform_point(g_sc.aabb_w2o, ray.Origin);
-        tl_ray.object_direction = xform_vector(g_sc.aabb_w2o, ray.Direction);
-        tl_ray.object_to_world = g_sc.aabb_o2w;
+        tl_ray.object_origin = xform_point(g_sc.aabb_insts[k].w2o, ray.Origin);
+        tl_ray.object_direction = xform_vector(g_sc.aabb_insts[k].w2o, ray.Direction);
+        tl_ray.object_to_world = g_sc.aabb_insts[k].o2w;
         const float3 o = tl_ray.object_origin;
         const float3 inv_d(1.0f / tl_ray.object_direction.x, 1.0f / tl_ray.object_direction.y, 1.0f / tl_ray.object_direction.z);
         if (!g_sc.use_bvh) {
             for (uint i = 0; i < (uint)g_sc.aabbs.size() && !done; i++) {
                 tl_counters.aabb_tests++;
                 if (slab_test(o, inv_d, &g_sc.aabbs[i].min_x, &g_sc.aabbs[i].max_x, ray.TMin, tcur))
-                    run_candidate(i, hit_group_offset, stride, first_hit, proc_hit, done);
+                    run_candidate(k, i, hit_group_offset, stride, first_hit, proc_hit, done);
             }
         } else {
             uint32_t cand[256];
@@ -378,8 +384,8 @@ static void trace_core(uint flags, uint hit_group_offset, uint stride, const Ray
                     if (ncand < 256) cand[ncand++] = (uint32_t)~n.left; else spill.push_back((uint32_t)~n.left);
                 } else { stack[sp++] = n.right; stack[sp++] = n.left; }
             }
-            if (!spill.empty()) { spill.insert(spill.end(), cand, cand + ncand); std::sort(spill.begin(), spill.end()); for (uint32_t g : spill) { if (done) break; run_candidate(g, hit_group_offset, stride, first_hit, proc_hit, done); } }
-            else { std::sort(cand, cand + ncand); for (uint32_t k = 0; k < ncand && !done; k++) run_candidate(cand[k], hit_group_offset, stride, first_hit, proc_hit, done); }
+            if (!spill.empty()) { spill.insert(spill.end(), cand, cand + ncand); std::sort(spill.begin(), spill.end()); for (uint32_t g : spill) { if (done) break; run_candidate(k, g, hit_group_offset, stride, first_hit, proc_hit, done); } }
+            else { std::sort(cand, cand + ncand); for (uint32_t c = 0; c < ncand && !done; c++) run_candidate(k, cand[c], hit_group_offset, stride, first_hit, proc_hit, done); }
         }
     }
 
@@ -387,7 +393,9 @@ static void trace_core(uint flags, uint hit_group_offset, uint stride, const Ray
     CommittedHit hit = tri_hit;
     if (proc_hit.kind && (!tri_hit.kind || proc_hit.t <= tri_hit.t)) hit = proc_hit;
     if (is_primary && PayloadOps<Payload>::radiance)
-        tl_primary_hit_id = hit.kind == 0 ? GPRT_HIT_MISS : hit.kind == 1 ? (GPRT_HIT_TRIANGLE | hit.index) : (GPRT_HIT_AABB | hit.index);
+        tl_primary_hit_id = hit.kind == 0 ? GPRT_HIT_MISS
+                          : hit.kind == 1 ? (GPRT_HIT_TRIANGLE | (hit.inst * (g_sc.n_indices / 3u) + hit.index))
+                                          : (GPRT_HIT_AABB | (hit.inst * (uint)g_sc.aabbs.size() + hit.index));
 
     if (hit.kind == 0) {
         PayloadOps<Payload>::miss(payload);
@@ -395,13 +403,13 @@ static void trace_core(uint flags, uint hit_group_offset, uint stride, const Ray
         tl_ray.tcurrent = hit.t;
         tl_ray.primitive_index = hit.kind == 1 ? hit.index : 0;
         if (hit.kind == 1) {
-            tl_ray.object_to_world = g_sc.tri_o2w;
-            bind_local_root(hit_record(hit_group_offset + stride * 0 + g_sc.tri_contrib));
+            tl_ray.object_to_world = g_sc.tri_insts[hit.inst].o2w;
+            bind_local_root(hit_record(hit_group_offset + stride * 0 + g_sc.tri_insts[hit.inst].contrib));
             BuiltInTriangleIntersectionAttributes a; a.barycentrics = hit.bary;
             PayloadOps<Payload>::closest_triangle(payload, a);
         } else {
-            tl_ray.object_to_world = g_sc.aabb_o2w;
-            bind_local_root(hit_record(hit_group_offset + stride * hit.index + g_sc.aabb_contrib));
+            tl_ray.object_to_world = g_sc.aabb_insts[hit.inst].o2w;
+            bind_local_root(hit_record(hit_group_offset + stride * hit.index + g_sc.aabb_insts[hit.inst].contrib));
             PayloadOps<Payload>::closest_aabb(payload, hit.attr);
         }
     }
@@ -456,10 +464,12 @@ int oracle_set_scene(const gprt_aabb* aabbs, uint32_t n_aabbs, const gprt_vertex
         float3x4 o2w;
         std::memcpy(o2w.m, instances[i].transform, sizeof o2w.m);
         uint contrib = instances[i].hit_group_contrib_and_flags & 0xFFFFFFu;
+        Scene::Inst inst;
+        inst.o2w = o2w; inst.w2o = invert_affine(o2w); inst.contrib = contrib;
         if (instances[i].acceleration_structure == GPRT_BLAS_TRIANGLES) {
-            g_sc.has_tri = n_indices >= 3; g_sc.tri_o2w = o2w; g_sc.tri_w2o = invert_affine(o2w); g_sc.tri_contrib = contrib;
+            g_sc.has_tri = n_indices >= 3; g_sc.tri_insts.push_back(inst);
         } else if (instances[i].acceleration_structure == GPRT_BLAS_AABBS) {
-            g_sc.has_aabb = n_aabbs > 0; g_sc.aabb_o2w = o2w; g_sc.aabb_w2o = invert_affine(o2w); g_sc.aabb_contrib = contrib;
+            g_sc.has_aabb = n_aabbs > 0; g_sc.aabb_insts.push_back(inst);
         } else return -1;
     }
     if (cfg) {

@@ -5,7 +5,7 @@ exists).  The reference ships no golden vectors of its own
 fixtures are the pin: the GPU path, the oracle port and any later rebuild of oracle/_ref are
 compared against them.
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py [fixture names: default all]
 
 Each fixture: the exact scene inputs are rebuilt from (scene_id, width, height, grid_n, time) by
 the host scene builder; stored are the RGBA8 image, the primary hit ids and the work counters.
@@ -34,6 +34,7 @@ FIXTURES = {
     "config4_t0": (4, 96, 54, 0, 0.0, None),
     "config4_t225": (4, 96, 54, 0, 2.25, None),
     "config5_grid24": (5, 128, 72, 24, 1.0, None),
+    "instanced_t1": (7, 160, 90, 0, 1.0, None),  # two-level instancing: 3 AABB instances, 2 triangle instances
 }
 
 
@@ -49,13 +50,15 @@ def render_fixture(name):
 
 
 def main():
-    meta = {}
-    for name in FIXTURES:
+    names = sys.argv[1:] or list(FIXTURES)
+    meta_path = os.path.join(HERE, "golden_meta.json")
+    meta = json.load(open(meta_path)) if (sys.argv[1:] and os.path.exists(meta_path)) else {}
+    for name in names:
         scene, res = render_fixture(name)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), rgba8=res["rgba8"], hit_ids=res["hit_ids"])
-        meta[name] = {"params": FIXTURES[name], "counters": res["counters"]}
+        meta[name] = {"params": list(FIXTURES[name]), "counters": res["counters"]}
         print(name, res["rgba8"].shape, res["counters"]["radiance_rays"], res["counters"]["shadow_rays"])
-    with open(os.path.join(HERE, "golden_meta.json"), "w") as f:
+    with open(meta_path, "w") as f:
         json.dump(meta, f, indent=1)
 
 

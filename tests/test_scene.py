@@ -60,6 +60,28 @@ def test_plane_and_instances(ref_scene):
     np.testing.assert_allclose(box["transform"], [[1, 0, 0, 0], [0, 1, 0, 1], [0, 0, 1, 0]])
 
 
+def test_instanced_scene_tlas_and_hit_groups():
+    """Scene 7 (two-level instancing): the reference primitives under a TLAS with three AABB instances and
+    two triangle instances; the first two TLAS entries and the first 22 records are the reference's."""
+    s = Renderer(scene_id=7, device=None).scene()
+    ref = Renderer(scene_id=0, device=None).scene()
+    assert len(s.instances) == 5 and len(s.aabbs) == 10
+    assert [int(i["acceleration_structure"]) for i in s.instances] == [0, 1, 1, 1, 0]
+    assert [int(i["hit_group_contrib_and_flags"]) & 0xFFFFFF for i in s.instances] == [0, 2, 2, 22, 42]
+    np.testing.assert_array_equal(s.instances[:2]["transform"], ref.instances["transform"])
+    assert len(s.hit_groups) == 2 + 20 + 20 + 2
+    assert s.hit_groups[:22].tobytes() == ref.hit_groups.tobytes()
+    a, b = s.hit_groups[2:22], s.hit_groups[22:42]
+    np.testing.assert_array_equal(a["shader_id"], b["shader_id"])
+    np.testing.assert_array_equal(a["instance_index"], b["instance_index"])
+    # the two 2x2x2 SDF primitives swap their intersection type in the second block
+    swapped = a["primitive_type"] != b["primitive_type"]
+    assert sorted(np.flatnonzero(swapped) // 2) == [3, 3, 4, 4]
+    # rotation + uniform scale 0.7 of the second AABB instance: rows of the 3x3 part have length 0.7
+    t = s.instances[2]["transform"][:, :3]
+    np.testing.assert_allclose(np.linalg.norm(t, axis=1), 0.7, rtol=1e-6)
+
+
 def test_camera_and_light(ref_scene):
     cb = ref_scene.scene_cb[0]
     np.testing.assert_allclose(cb["camera_position"], [-12.0208153, 5.3, -12.0208153, 1.0], rtol=1e-6)
