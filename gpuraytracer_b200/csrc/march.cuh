@@ -1,7 +1,7 @@
 // march.cuh -- candidate-queue plumbing shared by the intersection kernels (included by kernels.cu):
 // warp-aggregated queue reservation (warp_take), GetRayInAABBPrimitiveLocalSpace for one queue entry
-// (fetch_candidate), ReportHit (publish_hit), the closed-form analytic tests over their queues and the
-// one-candidate-per-lane baseline marcher (simple_queue).  The production marchers are in march_coop.cuh.
+// (fetch_candidate), ReportHit (publish_hit) and the closed-form analytic tests over their queues.
+// The marchers are in march_coop.cuh.
 #pragma once
 
 namespace gprt {
@@ -111,30 +111,6 @@ __device__ __forceinline__ void analytic_queue(const SceneDev& sc, const PassPar
                 work++;
                 const bool hit = (TYPE == 0) ? ray_unit_box(s.lr, thit, n) : ray_spheres(s.lr, thit, n);
                 if (hit) publish_hit<TYPE>(sc, wb, s, thit, n); else publish_miss<TYPE>(wb, s);
-            }
-        }
-        if (q.exhausted && q.next >= q.end) break;
-    }
-    for (int off = 16; off; off >>= 1) work += __shfl_xor_sync(kFull, work, off);
-    if (lane == 0 && work) atomicAdd(&ctrl->work[TYPE], work);
-}
-
-// One candidate per lane, run to completion, then the warp takes the next 32 (no state machine).
-template <int TYPE, int NB>
-__device__ __forceinline__ void simple_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
-    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
-    WarpChunk q;
-    uint32_t work = 0;
-    for (;;) {
-        const uint32_t idx = warp_take(q, true, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand) {
-            CandState s;
-            if (fetch_candidate<TYPE>(sc, wb, pq, idx, s)) {
-                float thit = 0.0f;
-                V3 n = v3s(0.0f);
-                Material m;
-                m.step_scale = s.step_scale;
-                if (run_test<TYPE, NB>(s.lr, m, pp, thit, n, work)) publish_hit<TYPE>(sc, wb, s, thit, n); else publish_miss<TYPE>(wb, s);
             }
         }
         if (q.exhausted && q.next >= q.end) break;

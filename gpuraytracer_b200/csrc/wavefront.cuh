@@ -5,10 +5,11 @@
 // (src/Raytracing.hlsl:154-165 and the TraceRay calls under it).  Here the tree is flattened into
 // `max_recursion_depth` WAVES.  Wave k holds the level-k radiance rays plus the level-(k-1)
 // shadow rays; for each wave:
-//   traverse      ray vs plane triangles, then LBVH walk -> (ray, primitive) candidates appended
-//                 to one queue per primitive type (warp-aggregated atomics)
-//   intersect<T>  one kernel per primitive type: the type's intersection test on every candidate,
-//                 64-bit atomicMin of (t, primitive) per ray
+//   traverse      ray vs plane triangles, then the LBVH walk (per TLAS instance) -> (ray, primitive)
+//                 candidates appended to one queue per primitive type; long walks are handed on to
+//                 spill rounds after a node budget
+//   intersect     one persistent launch: the type's intersection test on every candidate of
+//                 every queue, 64-bit atomicMin of (t, primitive) per ray
 //   resolve       the winning candidate of each ray publishes its normal
 //   shade_spawn   stores the level's hit record per pixel, emits the next wave's shadow and
 //                 reflection rays (ballot/popc compaction)
