@@ -303,6 +303,7 @@ int upload_static_scene(gprt_ctx* c) {
     s.aabb_insts = c->d_aabb_insts;
     s.plane_mats = c->d_plane_mats;
     s.leaf_types_valid = types_agree ? 1u : 0u;
+    s.inv_n_prims = n > 1 ? (~0ull / n) + 1ull : 0ull; // n == 1 is never divided by: flat is the instance then (see inst_xform)
     if (n_ti) std::memcpy(s.tri_w2o, tri_insts[0].w2o, sizeof s.tri_w2o);
     if (n_ai) {
         std::memcpy(s.aabb_w2o, aabb_insts[0].w2o, sizeof s.aabb_w2o);

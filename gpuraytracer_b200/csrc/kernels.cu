@@ -351,7 +351,8 @@ __device__ __forceinline__ InstXform inst_xform(const SceneDev& sc, uint32_t fla
     InstXform x;
     x.w2o = sc.aabb_w2o; x.o2w = sc.aabb_o2w;
     if (sc.n_aabb_insts > 1u) {
-        const uint32_t k = flat / sc.n_prims;
+        // flat / n_prims without the division sequence (inv == 0: one primitive, flat is the instance)
+        const uint32_t k = sc.inv_n_prims ? (uint32_t)__umul64hi((unsigned long long)flat, sc.inv_n_prims) : flat;
         if (k) { x.w2o = sc.aabb_insts[k].w2o; x.o2w = sc.aabb_insts[k].o2w; }
     }
     return x;

@@ -75,6 +75,7 @@ struct SceneDev {
     const InstDev* aabb_insts;   // [n_aabb_insts]
     const Material* plane_mats;  // [n_tri_insts]: the triangle hit group of each instance's contribution
     uint32_t leaf_types_valid;   // the type tag in the leaf refs holds for every AABB instance
+    unsigned long long inv_n_prims; // floor(2^64 / n_prims) + 1: flat / n_prims == __umul64hi(flat, inv_n_prims) for flat < 2^27
 };
 
 constexpr int kSpillRounds = 3; // traversal hand-over rounds after the main walk (the last one has no node budget)
