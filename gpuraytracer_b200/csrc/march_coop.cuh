@@ -69,10 +69,9 @@ __device__ __forceinline__ bool fetch_lane(const SceneDev& sc, const WaveBuffers
     m.c = c; m.r = cand.x;
     const float4 rd = wb.ray_d[pq][m.r];
     m.shadow = meta_shadow(__float_as_uint(rd.w)) != 0u;
-    if (m.shadow && wb.hitkey[m.r] != kKeyMiss) {
-        wb.cand_res[type][c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
-        return false;
-    }
+    // the result starts as "no hit": only publish_lane_hit writes again, the retire paths of the march loops write nothing
+    wb.cand_res[type][c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+    if (m.shadow && wb.hitkey[m.r] != kKeyMiss) return false;
     const float4 ro = wb.ray_o[pq][m.r];
     const PrimRecord* pr = sc.prims + cand.y;
     m.scale = pr->mat.step_scale;
@@ -98,8 +97,6 @@ __device__ __forceinline__ void publish_lane_hit(const SceneDev& sc, const WaveB
         const V3 nw = normalize(xform_vector_3x4(inst_xform(sc, prim).o2w, nb));
         atomicMin(&wb.hitkey[m.r], pack_key(thit, prim));
         wb.cand_res[type][m.c] = make_float4(nw.x, nw.y, nw.z, fabsf(thit));
-    } else {
-        wb.cand_res[type][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
     }
 }
 
@@ -111,7 +108,7 @@ __device__ __forceinline__ void poll_committed(const WaveBuffers& wb, int type, 
     if (!m.active) return;
     const unsigned long long key = __ldcg(&wb.hitkey[m.r]);
     if (key == kKeyMiss) return;
-    if (m.shadow) { wb.cand_res[type][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); m.active = false; }
+    if (m.shadow) m.active = false;
     else m.t_stop = fminf(m.t_stop, __uint_as_float((uint32_t)(key >> 32)));
 }
 
@@ -134,10 +131,7 @@ __device__ __forceinline__ uint32_t coop_trips(const int SDF, MarchLane& m, int 
 #pragma unroll 1
     for (int trip = 0; trip < trips; trip++) {
         // while (i++ < MaxSteps && t <= RayTCurrent())
-        if (m.active && m.mode == 0 && !(m.step < max_steps && m.t <= m.t_stop)) {
-            wb.cand_res[TYPE][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
-            m.active = false;
-        }
+        if (m.active && m.mode == 0 && !(m.step < max_steps && m.t <= m.t_stop)) m.active = false;
         const unsigned b1 = __ballot_sync(kFull, m.active && m.mode == 0), b5 = __ballot_sync(kFull, m.active && m.mode == 1);
         if (!(b1 | b5)) break;
         const uint32_t my_off = (uint32_t)__popc(b1 & lt) + 5u * (uint32_t)__popc(b5 & lt);
@@ -180,10 +174,8 @@ __device__ __forceinline__ uint32_t coop_trips(const int SDF, MarchLane& m, int 
                 } else {
                     m.t = t_next;
                     m.mode = 0;
-                    if (!(m.step < max_steps && m.t <= m.t_stop)) {
-                        wb.cand_res[TYPE][m.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
-                        m.active = false;
-                    } else { dist = sdist[my_off + 4]; have_sample = true; }
+                    if (!(m.step < max_steps && m.t <= m.t_stop)) m.active = false;
+                    else { dist = sdist[my_off + 4]; have_sample = true; }
                 }
             }
             if (have_sample) {
@@ -298,8 +290,7 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
         uint32_t mask = 0;
         if (idx != kNoCand && fetch_lane(sc, wb, pq, TYPE, idx, m)) {
             mask = find_metaball_span<NB>(m.o, m.d, 0.0f, m.tcur, mb, tmin, tmax);
-            if (tmin == __builtin_inff()) wb.cand_res[TYPE][idx] = make_float4(0.0f, 0.0f, 0.0f, -1.0f); // field is 0 at every sample
-            else keep = true;
+            keep = tmin != __builtin_inff(); // otherwise the field is 0 at every sample
         }
         const unsigned kb = __ballot_sync(kFull, keep);
         const int n_list = __popc(kb);
@@ -359,7 +350,6 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
                 // next pass starts one step after lane 31's sample
                 t_base = __shfl_sync(kFull, t, 31) + dt;
             }
-            if (!done && lane == 0) wb.cand_res[TYPE][r.c] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
             work += steps_done;
         }
         __syncwarp();
