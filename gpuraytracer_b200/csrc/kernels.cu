@@ -539,7 +539,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_spawn(const __grid_constant__ 
 // final_color: fold the per-level hit records back to front -- the order in which the recursive
 // closest-hit / miss shaders return -- and store R8G8B8A8_UNORM (src/Raytracing.hlsl:164).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_final_color(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kBlock, 5) k_final_color(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                         const __grid_constant__ WaveBuffers wb, const __grid_constant__ OutputBuffers ob) {
     for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < pp.n_pixels; pixel += gridDim.x * blockDim.x) {
         const uint32_t tx = pixel % pp.tile_w, ty = pixel / pp.tile_w;
