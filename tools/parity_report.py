@@ -10,7 +10,8 @@ from tests.parity import report
 CASES = [("config1 640x480", 1, 0, 0, 0, 0.0), ("config2 1920x1080 t=0", 2, 0, 0, 0, 0.0), ("config2 1920x1080 t=3", 2, 0, 0, 0, 3.0),
          ("config3 960x540", 3, 960, 540, 0, 0.0), ("config3 long budget 480x270", 6, 480, 270, 0, 0.0),
          ("config4 1920x1080 t=2.25", 4, 0, 0, 0, 2.25), ("config4 1920x1080 t=9", 4, 0, 0, 0, 9.0),
-         ("config5 grid 64 1920x1080", 5, 1920, 1080, 64, 1.0)]
+         ("config5 grid 64 1920x1080", 5, 1920, 1080, 64, 1.0), ("config5 grid 256 (65536 primitives, spill rounds on) 1920x1080", 5, 1920, 1080, 256, 1.0),
+         ("instanced scene 7 (3 AABB + 2 triangle instances) 1920x1080 t=1", 7, 1920, 1080, 0, 1.0)]
 out = {"math_mode": "fast" if "--fast" in sys.argv else "parity", "rule": ">= 99.9 % of pixels within 2/255 per channel; interior hit ids equal", "cases": {}}
 for name, sid, w, h, g, t in CASES:
     cfg = default_config()
