@@ -366,7 +366,7 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
 // the warps resident on one SM run the same code (measured: with a per-warp rotation
 // stall_no_instruction became the top stall).
 template <int NB, int RMIN>
-__global__ void __launch_bounds__(kBlock, 3) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kBlock, 4) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
     __shared__ CoopSmem sm;
     WaveCtrl* ctrl = &wb.ctrl[wave];
