@@ -119,6 +119,8 @@ def lib():
         "gprt_last_cuda_error": (i32, [vp]),
         "gprt_set_stream": (i32, [vp, vp]),
         "gprt_last_launch_count": (i32, [vp]),
+        "gprt_alloc_host": (vp, [C.c_size_t]),
+        "gprt_free_host": (None, [vp]),
         "gprt_error_string": (C.c_char_p, [i32]),
         "gprt_abi_version": (u32, []),
         "gprt_renderer_create": (i32, [C.POINTER(vp), i32, u32, u32, u32, i32, C.POINTER(Config)]),
@@ -158,7 +160,7 @@ def lib():
 
 
 EXPORTED_SYMBOLS = [
-    "gprt_default_config", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
+    "gprt_default_config", "gprt_alloc_host", "gprt_free_host", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
     "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_dispatch_host_async", "gprt_get_stream", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",

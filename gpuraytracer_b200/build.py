@@ -14,6 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 HOST = os.path.join(HERE, "host")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libgprt.so")
+CLI = os.path.join(HERE, "gprt_render")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-Xcompiler", "-fno-fast-math",
@@ -71,6 +72,13 @@ def build(verbose=False, force=False, ptxas_info=False):
         raise RuntimeError("nvcc failed")
     if force or procs or _newer(LIB, objs):
         cmd = ["nvcc", *ARCH, "-shared", "-o", LIB, *objs, "-cudart", "static"]
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+    # the headless CLI (host/gprt_render.cpp): plain C++ against the C ABI, finds libgprt.so next to itself
+    cli_src = os.path.join(HOST, "gprt_render.cpp")
+    if force or _newer(CLI, [cli_src, LIB] + HEADERS):
+        cmd = ["g++", "-O2", "-std=c++17", cli_src, "-o", CLI, "-L" + HERE, "-lgprt", "-Wl,-rpath,$ORIGIN"]
         if verbose:
             print(" ".join(cmd), flush=True)
         subprocess.check_call(cmd)

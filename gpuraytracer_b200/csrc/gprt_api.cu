@@ -791,4 +791,11 @@ int gprt_measure_fp32_peak(gprt_ctx* c, float* tflops_out) {
 int gprt_last_cuda_error(gprt_ctx* c) { return c ? c->last_cuda_error : 0; }
 int gprt_last_launch_count(gprt_ctx* c) { return c ? c->last_launches : 0; }
 
+void* gprt_alloc_host(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void gprt_free_host(void* p) { if (p) cudaFreeHost(p); }
+
 } // extern "C"

@@ -309,6 +309,11 @@ int gprt_set_stream(gprt_ctx* ctx, void* cuda_stream);
 /* Number of kernels launched by the last dispatch (for bench.py's gpu_launches). */
 int gprt_last_launch_count(gprt_ctx* ctx);
 
+/* Page-locked host memory for the frames of gprt_dispatch_host_async / the *_async renderer calls (cudaHostAlloc /
+ * cudaFreeHost), so that a host without the CUDA toolkit can keep copies asynchronous.  NULL on failure. */
+void* gprt_alloc_host(size_t bytes);
+void gprt_free_host(void* p);
+
 const char* gprt_error_string(int status);
 uint32_t gprt_abi_version(void);
 

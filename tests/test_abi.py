@@ -124,3 +124,19 @@ def test_write_ppm(tmp_path):
     write_ppm(p, img)
     data = open(p, "rb").read()
     assert data.startswith(b"P6\n6 4\n255\n") and len(data) == 11 + 6 * 4 * 3
+
+
+def test_headless_cli_exists_and_fails_loudly_without_a_gpu():
+    """gprt_render (host/gprt_render.cpp) is the stand-in for the reference's main.cpp + Window loop.  It links the
+    C ABI only; without a GPU it must fail with the library's "no device" error, not fall back to anything."""
+    import os
+    import subprocess
+    import torch
+    cli = os.path.join(os.path.dirname(_capi.__file__), "gprt_render")
+    assert os.path.exists(cli), "run __graft_entry__.build()"
+    out = subprocess.run([cli, "--help"], capture_output=True, text=True)
+    assert out.returncode == 0 and "--scene" in out.stdout
+    assert subprocess.run([cli, "--bogus"], capture_output=True).returncode == 2
+    if not torch.cuda.is_available():
+        out = subprocess.run([cli, "--scene", "0", "--width", "64", "--height", "36"], capture_output=True, text=True)
+        assert out.returncode == 1 and "no usable CUDA device" in out.stderr

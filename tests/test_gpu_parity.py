@@ -392,6 +392,28 @@ def test_error_behaviour_on_device():
             r.on_render(tile=(60, 30, 16, 16))                       # tile outside the dispatch
 
 
+def test_headless_cli_writes_the_frames_the_library_renders(tmp_path):
+    """gprt_render: 5 animated frames with 3 in flight, written as PPM; every file equals what Renderer.on_render
+    returns for that frame's time."""
+    import subprocess
+    cli = os.path.join(os.path.dirname(_capi.__file__), "gprt_render")
+    prefix = str(tmp_path / "f")
+    out = subprocess.run([cli, "--scene", "0", "--width", "160", "--height", "90", "--frames", "5", "--time", "0.5", "--dt", "0.25", "--out", prefix],
+                         capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "Million Primary Rays/s" in out.stdout
+    with Renderer(scene_id=0, width=160, height=90, device=0, config=make_cfg()) as r:
+        r.on_init()
+        for f in range(5):
+            r.on_update(0.5 + 0.25 * f)
+            img, _ = r.on_render()
+            data = open(f"{prefix}{f:04d}.ppm", "rb").read()
+            header = b"P6\n160 90\n255\n"
+            assert data.startswith(header)
+            ppm = np.frombuffer(data[len(header):], np.uint8).reshape(90, 160, 3)
+            np.testing.assert_array_equal(ppm, img[:, :, :3])
+
+
 def test_empty_and_degenerate_scenes():
     """No procedural primitives at all / a single one (LBVH root is a leaf)."""
     import ctypes as C
