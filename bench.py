@@ -398,9 +398,17 @@ def roofline(args, conf, device, cfg, world):
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     fin_bytes = W * H * (4 + depth * 4) + int(c.radiance_rays) * 49
     fin_dur = ms[GPRT_K_FINAL] * 1e-3
+    fin_traffic, fin_traffic_src = None, None
+    try:
+        if conf["scene_id"] == 2:
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_full_k_final_color.json")))
+            fin_traffic = round(cap["launches"][0]["dram_bytes_total"])
+            fin_traffic_src = "profiles/r01_ncu_full_k_final_color.json (dram__bytes_read.sum + dram__bytes_write.sum; the hit records shade_spawn just wrote are partly still in L2)"
+    except Exception:
+        pass
     hbm = {"bound": "hbm", "kernel": "k_final_color", "achieved": round(fin_bytes / fin_dur / 1e9, 1) if fin_dur > 0 else 0.0, "peak": hbm_peak,
-           "unit": "GB/s", "frac": round(fin_bytes / fin_dur / 1e9 / hbm_peak, 4) if fin_dur > 0 else 0.0, "traffic": None,
-           "peak_source": hbm_src, "bytes_per_launch": fin_bytes}
+           "unit": "GB/s", "frac": round(fin_bytes / fin_dur / 1e9 / hbm_peak, 4) if fin_dur > 0 else 0.0, "traffic": fin_traffic,
+           "traffic_source": fin_traffic_src, "peak_source": hbm_src, "bytes_per_launch": fin_bytes}
     return roof, hbm, kernel_ms
 
 
