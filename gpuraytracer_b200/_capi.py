@@ -11,11 +11,12 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgprt.so")
 
-GPRT_ABI_VERSION = 1
-GPRT_MATH_PARITY, GPRT_MATH_FAST = 0, 1
+GPRT_ABI_VERSION = 2
+GPRT_MATH_PARITY, GPRT_MATH_FAST, GPRT_MATH_FMA = 0, 1, 2
 GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1
 GPRT_FLAG_PROFILE_KERNELS = 2
-GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14, 15
+GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL = 0, 1, 11, 12, 13, 14
+GPRT_K_INTERSECT_TAIL, GPRT_K_COUNT = 15, 16
 GPRT_HIT_MISS = 0xFFFFFFFF
 GPRT_HIT_TRIANGLE = 0x00000000
 GPRT_HIT_AABB = 0x10000000
@@ -29,7 +30,7 @@ GPRT_E_NOT_BUILT, GPRT_E_QUEUE_OVERFLOW, GPRT_E_UNSUPPORTED, GPRT_E_ABI_MISMATCH
 class Config(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("max_recursion_depth", C.c_uint32), ("metaballs_count", C.c_uint32),
                 ("metaball_max_steps", C.c_uint32), ("sdf_max_steps", C.c_uint32), ("math_mode", C.c_uint32),
-                ("cand_per_ray", C.c_uint32), ("flags", C.c_uint32)]
+                ("cand_per_ray", C.c_uint32), ("flags", C.c_uint32), ("fractal_iterations", C.c_uint32)]
 
 
 class Rect(C.Structure):
@@ -42,7 +43,7 @@ class Counters(C.Structure):
 
 
 class KernelProfile(C.Structure):
-    _fields_ = [("ms", C.c_float * 15), ("launches", C.c_uint32 * 15), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
+    _fields_ = [("ms", C.c_float * 16), ("launches", C.c_uint32 * 16), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
 
 
 class WaveStats(C.Structure):
@@ -67,7 +68,7 @@ class SceneView(C.Structure):
 
 # numpy views of the ABI structs (sizes asserted against include/gprt.h in tests/test_abi.py)
 KERNEL_NAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
-                "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final", "intersect_all"]
+                "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final", "intersect_all", "intersect_tail"]
 TYPE_NAMES = KERNEL_NAMES[1:11]
 
 SCENE_CB_DTYPE = np.dtype([("projection_to_world", "<f4", (4, 4)), ("camera_position", "<f4", 4), ("light_position", "<f4", 4),
@@ -108,9 +109,11 @@ def lib():
         "gprt_dispatch_stripes": (i32, [vp, vp, vp, u32, u32, u32, u32, u32, u32, vp, C.c_size_t, vp]),
         "gprt_stripe_local_rows": (u32, [u32, u32, u32, u32]),
         "gprt_dispatch_host_async": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp]),
+        "gprt_dispatch_stripes_host_async": (i32, [vp, vp, vp, u32, u32, u32, u32, u32, u32, vp, C.c_size_t]),
         "gprt_get_stream": (vp, [vp]),
         "gprt_dispatch_host": (i32, [vp, vp, vp, u32, u32, u32, Rect, vp, C.c_size_t, vp]),
         "gprt_sync": (i32, [vp]),
+        "gprt_poll_status": (i32, [vp]),
         "gprt_get_counters": (i32, [vp, C.POINTER(Counters)]),
         "gprt_last_timing": (i32, [vp, C.POINTER(Timing)]),
         "gprt_get_kernel_profile": (i32, [vp, C.POINTER(KernelProfile)]),
@@ -133,6 +136,7 @@ def lib():
         "gprt_renderer_on_render_async": (i32, [vp, vp]),
         "gprt_renderer_do_raytracing_async": (i32, [vp, vp]),
         "gprt_renderer_do_raytracing_stripes_async": (i32, [vp, u32, u32, u32, vp]),
+        "gprt_renderer_on_render_stripes_async": (i32, [vp, u32, u32, u32, vp]),
         "gprt_renderer_create_frame_contexts": (i32, [vp]),
         "gprt_renderer_set_frame_count": (i32, [vp, i32]),
         "gprt_renderer_get_frame_count": (i32, [vp]),
@@ -150,6 +154,10 @@ def lib():
         "gprt_renderer_context": (vp, [vp]),
         "gprt_renderer_primary_mrays_per_s": (f32, [vp]),
         "gprt_write_ppm": (i32, [C.c_char_p, vp, u32, u32]),
+        "gprt_scene_create": (i32, [C.POINTER(vp), i32, u32, u32, u32]),
+        "gprt_scene_destroy": (None, [vp]),
+        "gprt_scene_update": (i32, [vp, f32, f32, f32]),
+        "gprt_scene_get": (i32, [vp, C.POINTER(SceneView)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)  # AttributeError if the library does not export it
@@ -161,14 +169,15 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "gprt_default_config", "gprt_alloc_host", "gprt_free_host", "gprt_create", "gprt_destroy", "gprt_set_geometry", "gprt_set_hit_group_table", "gprt_build_accel",
-    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_dispatch_host_async", "gprt_get_stream", "gprt_sync", "gprt_get_counters", "gprt_last_timing",
+    "gprt_refit_accel", "gprt_dispatch", "gprt_dispatch_stripes", "gprt_stripe_local_rows", "gprt_dispatch_host", "gprt_dispatch_host_async", "gprt_dispatch_stripes_host_async", "gprt_get_stream", "gprt_sync", "gprt_poll_status", "gprt_get_counters", "gprt_last_timing",
     "gprt_get_kernel_profile", "gprt_get_wave_stats", "gprt_measure_fp32_peak", "gprt_last_cuda_error", "gprt_set_stream", "gprt_last_launch_count", "gprt_error_string", "gprt_abi_version",
     "gprt_renderer_create", "gprt_renderer_destroy", "gprt_renderer_on_init", "gprt_renderer_on_update", "gprt_renderer_on_render",
     "gprt_renderer_do_raytracing", "gprt_renderer_do_raytracing_stripes", "gprt_renderer_on_render_async", "gprt_renderer_do_raytracing_async",
-    "gprt_renderer_do_raytracing_stripes_async", "gprt_renderer_create_frame_contexts", "gprt_renderer_set_frame_count", "gprt_renderer_get_frame_count", "gprt_renderer_set_device_transforms", "gprt_renderer_get_device_transforms", "gprt_renderer_next_frame_slot",
+    "gprt_renderer_do_raytracing_stripes_async", "gprt_renderer_on_render_stripes_async", "gprt_renderer_create_frame_contexts", "gprt_renderer_set_frame_count", "gprt_renderer_get_frame_count", "gprt_renderer_set_device_transforms", "gprt_renderer_get_device_transforms", "gprt_renderer_next_frame_slot",
     "gprt_set_animation", "gprt_update_transforms", "gprt_get_transforms",
     "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_get_size", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
+    "gprt_scene_create", "gprt_scene_destroy", "gprt_scene_update", "gprt_scene_get",
 ]
 
 

@@ -15,16 +15,19 @@ HOST = os.path.join(HERE, "host")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libgprt.so")
 CLI = os.path.join(HERE, "gprt_render")
+SCENE_LIB = os.path.join(HERE, "libgprt_scene.so")  # the CUDA-free scene builder on its own (g++ only)
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-Xcompiler", "-fno-fast-math",
           "-Xcompiler", "-ffp-contract=off"]
 PARITY = ["--fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-DGPRT_KERNELS_PARITY"]
 FAST = ["--use_fast_math", "-DGPRT_KERNELS_FAST", "-DGPRT_FAST_MATH"]
+FMA = ["--fmad=true", "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-DGPRT_KERNELS_FMA"]
 
 UNITS = [
     (os.path.join(CSRC, "kernels.cu"), "kernels_parity.o", PARITY),
     (os.path.join(CSRC, "kernels.cu"), "kernels_fast.o", FAST),
+    (os.path.join(CSRC, "kernels.cu"), "kernels_fma.o", FMA),
     (os.path.join(CSRC, "lbvh.cu"), "lbvh.o", []),
     (os.path.join(CSRC, "fp32_probe.cu"), "fp32_probe.o", []),
     (os.path.join(CSRC, "transforms.cu"), "transforms.o", ["--fmad=false"]),
@@ -32,6 +35,7 @@ UNITS = [
     (os.path.join(CSRC, "gprt_common.cpp"), "gprt_common.o", []),
     (os.path.join(HOST, "scene.cpp"), "scene.o", []),
     (os.path.join(HOST, "renderer.cpp"), "renderer.o", []),
+    (os.path.join(HOST, "scene_capi.cpp"), "scene_capi.o", []),
 ]
 
 HEADERS = [os.path.join(CSRC, f) for f in ("vecmath.cuh", "prims.cuh", "shade.cuh", "wavefront.cuh", "march.cuh", "march_coop.cuh", "lbvh.h")] + \
@@ -72,6 +76,13 @@ def build(verbose=False, force=False, ptxas_info=False):
         raise RuntimeError("nvcc failed")
     if force or procs or _newer(LIB, objs):
         cmd = ["nvcc", *ARCH, "-shared", "-o", LIB, *objs, "-cudart", "static"]
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+    # the scene builder alone: plain g++, no CUDA runtime, nothing of the render path
+    scene_srcs = [os.path.join(HOST, "scene.cpp"), os.path.join(HOST, "scene_capi.cpp"), os.path.join(CSRC, "gprt_common.cpp")]
+    if force or _newer(SCENE_LIB, scene_srcs + HEADERS):
+        cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-fno-fast-math", "-ffp-contract=off", *scene_srcs, "-o", SCENE_LIB]
         if verbose:
             print(" ".join(cmd), flush=True)
         subprocess.check_call(cmd)

@@ -17,7 +17,14 @@ using namespace gprt;
 
 namespace {
 
-constexpr uint32_t kDefaultPassPixels = 1u << 22; // pixels per internal pass (bounds queue memory)
+// A frame is rendered in as few internal passes as the free HBM allows (one for everything up to 8K on an idle
+// 180 GB B200): every pass pays the per-wave latency floor (the slowest ray's dependent chain) once, so eight
+// serial bands of an 8K frame paid it eight times.  kPassMemoryFraction of the memory free at the moment a
+// context sizes its queues may go to them; GPRT_PASS_PIXELS overrides (tests force several passes with it).
+constexpr double kPassMemoryFraction = 0.55;
+constexpr uint32_t kMinPassPixels = 1u << 20;
+constexpr uint32_t kMaxPassPixelsSingle = (1u << 26) - 1u; // 26-bit pixel field of the ray meta word
+constexpr uint32_t kMaxPassPixelsMulti = 1u << 22;         // multi-instance spill entries pack the ray slot in kSpillRayBits
 constexpr int kStagingSlots = 3;                  // == frame_count of the reference (src/Renderer.h:92)
 constexpr int kMaxBands = 256;
 constexpr uint32_t kSpillBudget = 64;     // LBVH node fetches one thread spends on a ray before handing the rest of the walk on
@@ -49,6 +56,7 @@ struct gprt_ctx {
     PrimRecord* d_prims = nullptr;
     uint32_t spill_capacity_limit = 0; // GPRT_SPILL_CAPACITY (tests: forces the queue-full fallback of the walk)
     uint32_t spill_budget = 0;         // LBVH node fetches per thread before a walk is handed to the next spill round
+    uint32_t pass_pixel_override = 0;  // GPRT_PASS_PIXELS: pixels per internal pass (0 = from the free device memory)
     uint8_t* d_prim_types = nullptr;   // type id per primitive, tagged into the LBVH leaf refs
     float* d_per_frame = nullptr;
     uint32_t per_frame_capacity = 0;
@@ -92,6 +100,7 @@ struct gprt_ctx {
     int n_bands_last = 0;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_build0 = nullptr, ev_build1 = nullptr;
     bool have_dispatch_timing = false, have_build_timing = false;
+    bool overflow_reported = false; // the last dispatch's overflow has been returned to the caller once
     int last_launches = 0;
     uint32_t last_depth = 0;
 
@@ -159,6 +168,30 @@ template <class T> int alloc_pass(gprt_ctx* c, T** out, size_t count) {
     c->pass_allocs.push_back(p);
     *out = (T*)p;
     return GPRT_OK;
+}
+
+// Device bytes ensure_pass_buffers allocates per pixel of a pass (R = 2 P ray slots).
+size_t pass_bytes_per_pixel(const gprt_ctx* c) {
+    const size_t depth = c->cfg.max_recursion_depth;
+    const size_t per_ray = c->cfg.cand_per_ray ? c->cfg.cand_per_ray : 2u;
+    size_t n_types = 0;
+    for (int t = 0; t < kNumTypes; t++) n_types += (c->type_mask >> t) & 1u;
+    return 2 * (2 * 16 + 2 * 16 + 4 + 8 + 16) + n_types * 2 * per_ray * (8 + 16) + 2 * 8 + depth * (16 + 16 + 16 + 4 + 1);
+}
+
+// Most pixels one internal pass of this context may hold.
+uint32_t pass_pixel_limit(gprt_ctx* c) {
+    const bool multi = c->scene.n_tri_insts > 1u || c->scene.n_aabb_insts > 1u;
+    const uint32_t hard = multi ? kMaxPassPixelsMulti : kMaxPassPixelsSingle;
+    if (c->pass_pixel_override) return c->pass_pixel_override < hard ? c->pass_pixel_override : hard;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return kMinPassPixels; }
+    const size_t held = (size_t)c->pass_pixels * pass_bytes_per_pixel(c); // would be released first
+    const double budget = kPassMemoryFraction * (double)(free_b + held);
+    double px = budget / (double)pass_bytes_per_pixel(c);
+    if (px < (double)kMinPassPixels) px = (double)kMinPassPixels;
+    if (px > (double)hard) px = (double)hard;
+    return (uint32_t)px;
 }
 
 int ensure_pass_buffers(gprt_ctx* c, uint32_t pixels) {
@@ -354,6 +387,7 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     pp.max_depth = c->cfg.max_recursion_depth;
     pp.metaball_max_steps = c->cfg.metaball_max_steps;
     pp.sdf_max_steps = c->cfg.sdf_max_steps;
+    pp.fractal_iterations = c->cfg.fractal_iterations;
     pp.ray_capacity = 2 * pp.n_pixels;
     pp.cand_capacity = c->cand_capacity;
     pp.brute_force = (c->cfg.flags & GPRT_FLAG_BRUTE_FORCE_TRAVERSAL) ? 1u : 0u;
@@ -410,7 +444,9 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     if (c0.metaballs_count != 3 && c0.metaballs_count != 5) return GPRT_E_UNSUPPORTED;
     if (c0.metaball_max_steps == 0 || c0.sdf_max_steps == 0) return GPRT_E_INVALID_ARG;
     if (c0.metaball_max_steps > 0xFFFFu || c0.sdf_max_steps > 0xFFFFu) return GPRT_E_UNSUPPORTED; // march states pack the step count in 16 bits
-    if (c0.math_mode != GPRT_MATH_PARITY && c0.math_mode != GPRT_MATH_FAST) return GPRT_E_INVALID_ARG;
+    if (c0.math_mode != GPRT_MATH_PARITY && c0.math_mode != GPRT_MATH_FAST && c0.math_mode != GPRT_MATH_FMA) return GPRT_E_INVALID_ARG;
+    if (c0.fractal_iterations == 0) c0.fractal_iterations = 4; // FRACTAL_ITERATIONS_COUNT, src/ConstantBuffers.h:27
+    if (c0.fractal_iterations > 8) return GPRT_E_UNSUPPORTED;
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
     if (device_ordinal < 0 || device_ordinal >= n_dev) return GPRT_E_NO_DEVICE;
@@ -425,9 +461,10 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     // filter and shading stay IEEE: their cancellations (ray differentials, frac/floor at the grid
     // lines) do not survive approximate division.
     c->kt = kernels_parity();
-    c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : kernels_parity();
+    c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : (c0.math_mode == GPRT_MATH_FMA) ? kernels_fma() : kernels_parity();
     { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
     { const char* e = getenv("GPRT_SPILL_BUDGET"); c->spill_budget = e ? (uint32_t)atoi(e) : kSpillBudget; } // tuning aid
+    { const char* e = getenv("GPRT_PASS_PIXELS"); c->pass_pixel_override = e ? (uint32_t)atoll(e) : 0u; }
     { const char* e = getenv("GPRT_SPILL_CAPACITY"); c->spill_capacity_limit = e ? (uint32_t)atoi(e) : 0u; }
     std::memset(&c->scene, 0, sizeof c->scene);
     std::memset(&c->wb, 0, sizeof c->wb);
@@ -549,6 +586,13 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
     if (pitch_bytes < (size_t)tile.w * 4 || (pitch_bytes & 3u)) return GPRT_E_INVALID_ARG;
     if (n_per_frame && !per_frame) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaSetDevice(c->device));
+    // A caller of the asynchronous device-output path may synchronise its own stream and never call gprt_sync: an
+    // overflow of the PREVIOUS dispatch is reported here, once, before its control blocks are overwritten.
+    if (c->have_dispatch_timing && !c->overflow_reported) {
+        GPRT_CUDA(c, cudaEventSynchronize(c->ev_stop));
+        if (check_overflow(c) != GPRT_OK) { c->overflow_reported = true; return GPRT_E_QUEUE_OVERFLOW; }
+    }
+    c->overflow_reported = false;
 
     // every primitive's instance_index must address the transforms: uploaded now, or already on the device
     // (gprt_update_transforms / an earlier upload) when per_frame is NULL
@@ -581,11 +625,19 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
     }
     c->scene.per_frame = c->d_per_frame;
 
-    // internal passes bound the queue memory: at most kDefaultPassPixels pixels each
+    // internal passes bound the queue memory: as few equal row bands as the pass-size limit allows
     const uint64_t tile_pixels = (uint64_t)tile.w * tile.h;
     uint32_t band_h = tile.h;
-    if (tile_pixels > kDefaultPassPixels) { band_h = kDefaultPassPixels / tile.w; if (band_h == 0) band_h = 1; }
-    if ((uint64_t)band_h * tile.w >= (1u << 26)) return GPRT_E_UNSUPPORTED;
+    if (tile_pixels > c->pass_pixels) { // the queues in place do not hold the tile: size them (again) from the free memory
+        const uint64_t limit = pass_pixel_limit(c);
+        if (tile_pixels > limit) {
+            const uint64_t n_pass = (tile_pixels + limit - 1) / limit;
+            band_h = (uint32_t)((tile.h + n_pass - 1) / n_pass);
+            while (band_h > 1 && (uint64_t)band_h * tile.w > limit) band_h--;
+        }
+    }
+    if ((uint64_t)band_h * tile.w > kMaxPassPixelsSingle) return GPRT_E_UNSUPPORTED; // one row wider than a pass can be
+    if ((tile.h + band_h - 1) / band_h > (uint32_t)kMaxBands) return GPRT_E_UNSUPPORTED;
     int rc = ensure_pass_buffers(c, band_h * tile.w);
     if (rc != GPRT_OK) return rc;
 
@@ -662,6 +714,43 @@ int gprt_dispatch_host_async(gprt_ctx* c, const gprt_scene_cb* scene, const gprt
     return GPRT_OK;
 }
 
+int gprt_dispatch_stripes_host_async(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
+                                     uint32_t width, uint32_t height, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* h_frame_rgba8,
+                                     size_t frame_pitch_bytes) {
+    if (!c || !h_frame_rgba8 || width == 0 || height == 0) return GPRT_E_INVALID_ARG;
+    if (stripe_rows == 0 || world == 0 || rank >= world || frame_pitch_bytes < (size_t)width * 4) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t rows = gprt_stripe_local_rows(height, stripe_rows, rank, world);
+    if (rows == 0) return GPRT_OK;
+    const size_t pixels = (size_t)width * rows;
+    if (c->fb_pixels < pixels) {
+        cudaStreamSynchronize(c->stream);
+        cudaFree(c->d_fb); cudaFree(c->d_fb_ids); c->d_fb = nullptr; c->d_fb_ids = nullptr; c->fb_pixels = 0;
+        GPRT_CUDA(c, cudaMalloc((void**)&c->d_fb, pixels * 4));
+        GPRT_CUDA(c, cudaMalloc((void**)&c->d_fb_ids, pixels * 4));
+        c->fb_pixels = pixels;
+    }
+    const size_t row_bytes = (size_t)width * 4;
+    int rc = gprt_dispatch_stripes(c, scene, per_frame, n_per_frame, width, height, stripe_rows, rank, world, c->d_fb, row_bytes, nullptr);
+    if (rc != GPRT_OK) return rc;
+    // local stripe k (stripe_rows packed rows) is global stripe k * world + rank: the whole stripes leave in ONE strided copy
+    // (a "row" of the 2D copy is a stripe when the frame is tightly pitched, a pixel row otherwise), a partial last one after it
+    char* dst0 = (char*)h_frame_rgba8 + (size_t)rank * stripe_rows * frame_pitch_bytes;
+    const uint32_t whole = rows / stripe_rows, tail = rows % stripe_rows;
+    if (frame_pitch_bytes == row_bytes) {
+        const size_t stripe_bytes = (size_t)stripe_rows * row_bytes;
+        if (whole) GPRT_CUDA(c, cudaMemcpy2DAsync(dst0, stripe_bytes * world, c->d_fb, stripe_bytes, stripe_bytes, whole, cudaMemcpyDeviceToHost, c->stream));
+    } else {
+        for (uint32_t k = 0; k < whole; k++)
+            GPRT_CUDA(c, cudaMemcpy2DAsync(dst0 + (size_t)k * world * stripe_rows * frame_pitch_bytes, frame_pitch_bytes,
+                                           c->d_fb + (size_t)k * stripe_rows * row_bytes, row_bytes, row_bytes, stripe_rows, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (tail)
+        GPRT_CUDA(c, cudaMemcpy2DAsync(dst0 + (size_t)whole * world * stripe_rows * frame_pitch_bytes, frame_pitch_bytes,
+                                       c->d_fb + (size_t)whole * stripe_rows * row_bytes, row_bytes, row_bytes, tail, cudaMemcpyDeviceToHost, c->stream));
+    return GPRT_OK;
+}
+
 int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_frame* per_frame, uint32_t n_per_frame, uint32_t width,
                        uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
     const int rc = gprt_dispatch_host_async(c, scene, per_frame, n_per_frame, width, height, tile, h_rgba8, pitch_bytes, h_hit_ids);
@@ -673,6 +762,15 @@ void* gprt_get_stream(gprt_ctx* c) { return c ? (void*)c->stream : nullptr; }
 int gprt_sync(gprt_ctx* c) {
     if (!c) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return check_overflow(c);
+}
+
+int gprt_poll_status(gprt_ctx* c) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    if (!c->have_dispatch_timing) return GPRT_OK;
+    const cudaError_t q = cudaEventQuery(c->ev_stop); // recorded after the last pass's control block went to the host
+    if (q == cudaErrorNotReady) return GPRT_OK;
+    if (q != cudaSuccess) { c->last_cuda_error = (int)q; return GPRT_E_CUDA; }
     return check_overflow(c);
 }
 

@@ -13,6 +13,7 @@ void gprt_default_config(gprt_config* cfg) {
     cfg->math_mode = GPRT_MATH_PARITY;
     cfg->cand_per_ray = 0;
     cfg->flags = 0;
+    cfg->fractal_iterations = 4;  // FRACTAL_ITERATIONS_COUNT, src/ConstantBuffers.h:27
 }
 
 uint32_t gprt_abi_version(void) { return GPRT_ABI_VERSION; }

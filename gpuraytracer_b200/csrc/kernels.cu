@@ -1,6 +1,7 @@
 // kernels.cu -- the wavefront kernels.  Compiled twice into libgprt.so:
 //   -DGPRT_KERNELS_PARITY   --fmad=false                  (IEEE, oracle-exact arithmetic)
 //   -DGPRT_KERNELS_FAST     --use_fast_math -DGPRT_FAST_MATH
+//   -DGPRT_KERNELS_FMA      --fmad=true, IEEE div/sqrt, no flush-to-zero (march kernels only)
 // See wavefront.cuh for the pipeline; prims.cuh / shade.cuh for the math and the reference
 // file:line each piece follows.
 #include <cuda_runtime.h>
@@ -137,10 +138,12 @@ __device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassPara
         if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
             if (ref0 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref0, pend);
             else if (tail - head < 64u) ring[tail++ & 63u] = ref0;
+            else ctrl->overflow = 1u; // never drop a subtree silently: the dispatch reports GPRT_E_QUEUE_OVERFLOW
         }
         if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
             if (ref1 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref1, pend);
             else if (tail - head < 64u) ring[tail++ & 63u] = ref1;
+            else ctrl->overflow = 1u;
         }
     }
     return visits;
@@ -363,7 +366,7 @@ __device__ __forceinline__ bool run_test(const LocalRay& lr, const Material& mat
     if (TYPE == 0) { work++; return ray_unit_box(lr, thit, n); }
     if (TYPE == 1) { work++; return ray_spheres(lr, thit, n); }
     if (TYPE == 2) return ray_metaballs<NB>(lr, pp.fc.elapsed_time, pp.metaball_max_steps, thit, n, work);
-    return ray_sdf<(TYPE >= 3 ? TYPE - 3 : 0)>(lr, mat.step_scale, pp.sdf_max_steps, thit, n, work);
+    return ray_sdf<(TYPE >= 3 ? TYPE - 3 : 0)>(lr, mat.step_scale, pp.sdf_max_steps, thit, n, work, pp.fractal_iterations);
 }
 
 template <int TYPE, int NB>
@@ -709,7 +712,12 @@ int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffe
 
 } // namespace
 
-#if defined(GPRT_KERNELS_FAST)
+#if defined(GPRT_KERNELS_FMA)
+const KernelTable* kernels_fma() {
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "fma"};
+    return &t;
+}
+#elif defined(GPRT_KERNELS_FAST)
 const KernelTable* kernels_fast() {
     static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "fast"};
     return &t;

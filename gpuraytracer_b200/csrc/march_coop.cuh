@@ -36,7 +36,7 @@ struct CoopSmem { // warp-private scratch
 
 // GetDistanceFromSignedDistancePrimitive with a run-time (warp-uniform) primitive type: one copy of
 // the march loop serves all seven SDF types; the branch is uniform, so it costs a jump.
-__device__ __forceinline__ float sdf_distance_dyn(int sdf, V3 p) {
+__device__ __forceinline__ float sdf_distance_dyn(int sdf, V3 p, uint32_t fractal_iters) {
     switch (sdf) {
     case 0: return sdf_distance<0>(p);
     case 1: return sdf_distance<1>(p);
@@ -44,7 +44,7 @@ __device__ __forceinline__ float sdf_distance_dyn(int sdf, V3 p) {
     case 3: return sdf_distance<3>(p);
     case 4: return sdf_distance<4>(p);
     case 5: return sdf_distance<5>(p);
-    default: return sdf_distance<6>(p);
+    default: return sdf_distance<6>(p, fractal_iters);
     }
 }
 
@@ -154,7 +154,7 @@ __device__ __forceinline__ uint32_t coop_trips(const int SDF, MarchLane& m, int 
             }
         }
         __syncwarp();
-        for (uint32_t j = lane; j < total; j += 32u) sdist[j] = sdf_distance_dyn(SDF, v3(spx[j], spy[j], spz[j])); // the one evaluation site
+        for (uint32_t j = lane; j < total; j += 32u) sdist[j] = sdf_distance_dyn(SDF, v3(spx[j], spy[j], spz[j]), pp.fractal_iterations); // the one evaluation site
         __syncwarp();
         if (m.active) {
             bool have_sample = false;

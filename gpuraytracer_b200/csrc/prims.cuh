@@ -286,27 +286,40 @@ GPRT_HD float sd_pyramid(V3 p, V3 h) { // sdOctahedron + opS(octa, p.y)
     const float octa = d - h.y * h.z;
     return fmaxf(octa, -p.y);
 }
-// sdFractalPyramid, src/SignedDistanceFractals.hlsli:34-63; FRACTAL_ITERATIONS_COUNT = 4, Scale = 2
-GPRT_HD float sd_fractal_pyramid(V3 p, V3 h) {
+// sdFractalPyramid, src/SignedDistanceFractals.hlsli:34-63; Scale = 2.  One fold towards the nearest of the five
+// vertices: position = Scale * position - v * (Scale - 1).
+GPRT_HD V3 fractal_fold(V3 p, float a, float hz) {
+    const V3 v1 = v3(0, hz, 0), v2_ = v3(-a, 0, a), v3_ = v3(a, 0, -a), v4_ = v3(a, 0, a), v5_ = v3(-a, 0, -a);
+    V3 v = v1;
+    V3 q = p - v1;
+    float dist = dot(q, q), d;
+    q = p - v2_; d = dot(q, q); if (d < dist) { v = v2_; dist = d; }
+    q = p - v3_; d = dot(q, q); if (d < dist) { v = v3_; dist = d; }
+    q = p - v4_; d = dot(q, q); if (d < dist) { v = v4_; dist = d; }
+    q = p - v5_; d = dot(q, q); if (d < dist) { v = v5_; dist = d; }
+    return v3s(2.0f) * p - v * v3s(2.0f - 1.0f);
+}
+// `iters` = FRACTAL_ITERATIONS_COUNT (src/ConstantBuffers.h:27; 4 in the reference, a run-time knob here, <= 8).
+GPRT_HD float sd_fractal_pyramid(V3 p, V3 h, uint32_t iters) {
     const float a = h.z * h.y / h.x;
-    const V3 v1 = v3(0, h.z, 0), v2_ = v3(-a, 0, a), v3_ = v3(a, 0, -a), v4_ = v3(a, 0, a), v5_ = v3(-a, 0, -a);
+    if (iters == 4u) { // the reference's value: fully unrolled
 #pragma unroll
-    for (int n = 0; n < 4; n++) {
-        V3 v = v1;
-        V3 q = p - v1;
-        float dist = dot(q, q), d;
-        q = p - v2_; d = dot(q, q); if (d < dist) { v = v2_; dist = d; }
-        q = p - v3_; d = dot(q, q); if (d < dist) { v = v3_; dist = d; }
-        q = p - v4_; d = dot(q, q); if (d < dist) { v = v4_; dist = d; }
-        q = p - v5_; d = dot(q, q); if (d < dist) { v = v5_; dist = d; }
-        p = v3s(2.0f) * p - v * v3s(2.0f - 1.0f);
+        for (int n = 0; n < 4; n++) p = fractal_fold(p, a, h.z);
+    } else {
+#pragma unroll 1
+        for (uint32_t n = 0; n < iters; n++) p = fractal_fold(p, a, h.z);
     }
-    // pow(Scale, -n) = exp2(log2(2) * -4) = 2^-4 exactly
-    return sd_pyramid(p, h) * 0.0625f;
+    // pow(Scale, -n) = exp2(log2(2) * -n) = 2^-n exactly
+#if defined(__CUDA_ARCH__)
+    const float inv_scale = __uint_as_float((127u - iters) << 23);
+#else
+    const float inv_scale = ldexpf(1.0f, -(int)iters);
+#endif
+    return sd_pyramid(p, h) * inv_scale;
 }
 
 // GetDistanceFromSignedDistancePrimitive, src/ProceduralPrimitivesLibrary.hlsli:63-98
-template <int TYPE> GPRT_HD float sdf_distance(V3 p) {
+template <int TYPE> GPRT_HD float sdf_distance(V3 p, uint32_t fractal_iters = 4u) {
     if (TYPE == 0) { // MiniSpheres
         return fmaxf(sd_sphere(op_rep(p + v3s(1.0f), v3s(2.0f) / v3s(4.0f)), 0.65f / 4.0f), sd_box(p, v3s(1.0f)));
     } else if (TYPE == 1) { // IntersectedRoundCube: opS(opS(roundbox, sphere 1.20), -sphere 1.32)
@@ -322,30 +335,31 @@ template <int TYPE> GPRT_HD float sdf_distance(V3 p) {
     } else if (TYPE == 5) { // Cylinder
         return fmaxf(sd_cylinder(op_rep(p + v3(1, 1, 1), v3(1, 2, 1)), v2(0.3f, 2.0f)), sd_box(p + v3(1, 1, 1), v3(2, 2, 2)));
     } else if (TYPE == 6) { // FractalPyramid
-        return sd_fractal_pyramid(p + v3(0, 1, 0), v3(0.894f, 0.447f, 2.0f));
+        return sd_fractal_pyramid(p + v3(0, 1, 0), v3(0.894f, 0.447f, 2.0f), fractal_iters);
     }
     return 0.0f;
 }
 
 // sdCalculateNormal (tetrahedral taps), src/SignedDistancePrimitives.hlsli:275-284
-template <int TYPE> GPRT_HD V3 sdf_normal(V3 pos) {
+template <int TYPE> GPRT_HD V3 sdf_normal(V3 pos, uint32_t fractal_iters = 4u) {
     const float ex = 1.0f * 0.5773f * 0.0001f, ey = -1.0f * 0.5773f * 0.0001f;
     const V3 xyy = v3(ex, ey, ey), yyx = v3(ey, ey, ex), yxy = v3(ey, ex, ey), xxx = v3(ex, ex, ex);
-    const V3 s = ((xyy * v3s(sdf_distance<TYPE>(pos + xyy)) + yyx * v3s(sdf_distance<TYPE>(pos + yyx))) + yxy * v3s(sdf_distance<TYPE>(pos + yxy))) +
-                 xxx * v3s(sdf_distance<TYPE>(pos + xxx));
+    const V3 s = ((xyy * v3s(sdf_distance<TYPE>(pos + xyy, fractal_iters)) + yyx * v3s(sdf_distance<TYPE>(pos + yyx, fractal_iters))) +
+                  yxy * v3s(sdf_distance<TYPE>(pos + yxy, fractal_iters))) +
+                 xxx * v3s(sdf_distance<TYPE>(pos + xxx, fractal_iters));
     return normalize(s);
 }
 
 // RaySignedDistancePrimitiveTest (sphere tracing), src/SignedDistancePrimitives.hlsli:287-319
-template <int TYPE> GPRT_HD bool ray_sdf(const LocalRay& r, float step_scale, uint32_t max_steps, float& thit, V3& n, uint32_t& work) {
+template <int TYPE> GPRT_HD bool ray_sdf(const LocalRay& r, float step_scale, uint32_t max_steps, float& thit, V3& n, uint32_t& work, uint32_t fractal_iters = 4u) {
     const float threshold = 0.0001f;
     float t = r.tmin;
     for (uint32_t i = 0; i < max_steps && t <= r.tcur; i++) {
         const V3 p = r.o + t * r.d;
-        const float distance = sdf_distance<TYPE>(p);
+        const float distance = sdf_distance<TYPE>(p, fractal_iters);
         work++;
         if (distance <= threshold * t) {
-            const V3 nn = sdf_normal<TYPE>(p);
+            const V3 nn = sdf_normal<TYPE>(p, fractal_iters);
             work += 4u;
             if (is_valid_hit(r, t, nn)) { thit = t; n = nn; return true; }
         }

@@ -100,6 +100,7 @@ struct PassParams {
     uint32_t tile_x, tile_y, tile_w, tile_h; // this pass's pixel rectangle (global coordinates)
     uint32_t n_pixels;                       // tile_w * tile_h
     uint32_t max_depth, metaball_max_steps, sdf_max_steps;
+    uint32_t fractal_iterations;             // FRACTAL_ITERATIONS_COUNT (src/ConstantBuffers.h:27)
     uint32_t ray_capacity;                   // 2 * n_pixels
     uint32_t cand_capacity;                  // per type
     uint32_t brute_force;
@@ -159,5 +160,6 @@ struct KernelTable {
 
 const KernelTable* kernels_parity();
 const KernelTable* kernels_fast();
+const KernelTable* kernels_fma(); // FMA contraction, IEEE div/sqrt, exact transcendentals
 
 } // namespace gprt

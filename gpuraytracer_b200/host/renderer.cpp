@@ -19,6 +19,7 @@ Renderer::Renderer(int scene_id, uint32_t width, uint32_t height, uint32_t grid_
         if (c.metaballs_count == 0) c.metaballs_count = m_scene.config.metaballs_count;
         if (c.metaball_max_steps == 0) c.metaball_max_steps = m_scene.config.metaball_max_steps;
         if (c.sdf_max_steps == 0) c.sdf_max_steps = m_scene.config.sdf_max_steps;
+        if (c.fractal_iterations == 0) c.fractal_iterations = m_scene.config.fractal_iterations;
         c.abi_version = GPRT_ABI_VERSION;
         m_scene.config = c;
     }
@@ -130,6 +131,21 @@ int Renderer::do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, u
     if (rc != GPRT_OK) return rc;
     return gprt_dispatch_stripes(c, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, stripe_rows, rank, world, d_rgba8,
                                  (size_t)m_scene.width * 4, nullptr);
+}
+
+int Renderer::on_render_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* h_frame_rgba8) {
+    int rc = ensure_frame_contexts();
+    if (rc != GPRT_OK) return rc;
+    gprt_ctx* c = m_frame_ctx[m_frame_index % (uint32_t)m_frame_count];
+    m_frame_index++;
+    rc = gprt_sync(c);
+    if (rc != GPRT_OK) return rc;
+    m_last_tile = {0, 0, m_scene.width, gprt_stripe_local_rows(m_scene.height, stripe_rows, rank, world)};
+    const gprt_prim_per_frame* pf; uint32_t npf;
+    rc = prepare_transforms(c, &pf, &npf);
+    if (rc != GPRT_OK) return rc;
+    return gprt_dispatch_stripes_host_async(c, &m_scene.scene_cb, pf, npf, m_scene.width, m_scene.height, stripe_rows, rank, world, h_frame_rgba8,
+                                            (size_t)m_scene.width * 4);
 }
 
 int Renderer::wait_for_gpu() {
@@ -279,6 +295,9 @@ int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned) { retu
 int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8) { return r ? r->impl.do_raytracing_async(d_rgba8) : GPRT_E_INVALID_ARG; }
 int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8) {
     return r ? r->impl.do_raytracing_stripes_async(stripe_rows, rank, world, d_rgba8) : GPRT_E_INVALID_ARG;
+}
+int gprt_renderer_on_render_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* h_frame_rgba8) {
+    return r ? r->impl.on_render_stripes_async(stripe_rows, rank, world, h_frame_rgba8) : GPRT_E_INVALID_ARG;
 }
 int gprt_renderer_get_device_transforms(gprt_renderer* r) { return r && r->impl.device_transforms() ? 1 : 0; }
 int gprt_renderer_set_device_transforms(gprt_renderer* r, int on) { if (!r) return GPRT_E_INVALID_ARG; r->impl.set_device_transforms(on != 0); return GPRT_OK; }

@@ -30,6 +30,8 @@ public:
     int on_render_async(void* h_rgba8_pinned);                   // on_render, 3 frames in flight, whole image
     int do_raytracing_async(void* d_rgba8);                      // same with device output
     int do_raytracing_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8); // multi-GPU, 3 in flight
+    // multi-GPU, host output: this rank's rows go straight to their global rows of a full-frame host buffer shared by all ranks
+    int on_render_stripes_async(uint32_t stripe_rows, uint32_t rank, uint32_t world, void* h_frame_rgba8);
     int create_frame_contexts() { return ensure_frame_contexts(); }
     int next_frame_slot() const { return (int)(m_frame_index % (uint32_t)m_frame_count); }
     // Frames in flight: 3 like the reference unless changed (1..kMaxFrameCount).  More slots hide the serial tail of a

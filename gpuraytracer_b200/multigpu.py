@@ -84,3 +84,62 @@ def compose(full, gathered, height: int, stripe_rows: int, world: int):
         else:
             full[rows] = gathered[r][:len(rows)]
     return full
+
+
+class SharedHostFrames:
+    """`n_slots` host buffers of `slot_bytes` that EVERY rank of the box can write with an asynchronous device-to-host
+    copy: POSIX shared memory mapped by all ranks and page-locked in each with cudaHostRegister (one rank: plain
+    page-locked memory).  Each rank then delivers its rows / frames over its own PCIe link straight into the frame the
+    host consumer (rank 0) reads, instead of all pixels funnelling through rank 0's GPU and its one link.  `barrier`
+    is called between creating, mapping and unlinking the file (dist.barrier on N ranks)."""
+
+    def __init__(self, tag: str, n_slots: int, slot_bytes: int, rank: int, world: int, barrier=None):
+        import mmap
+        import os
+
+        import torch
+        self.n_slots, self.slot_bytes, self.world = int(n_slots), int(slot_bytes), int(world)
+        self._registered = False
+        self._mm = None
+        total = self.n_slots * self.slot_bytes
+        if world <= 1:
+            self._t = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+            self.array = self._t.numpy()
+        else:
+            path = f"/dev/shm/gprt_{tag}"
+            if rank == 0:
+                fd = os.open(path, os.O_CREAT | os.O_RDWR | os.O_TRUNC, 0o600)
+                os.ftruncate(fd, total)
+                os.close(fd)
+            barrier()
+            fd = os.open(path, os.O_RDWR)
+            self._mm = mmap.mmap(fd, total)
+            os.close(fd)
+            self.array = np.frombuffer(self._mm, dtype=np.uint8)
+            err = torch.cuda.cudart().cudaHostRegister(self.array.ctypes.data, total, 0)
+            if int(err) != 0:
+                raise RuntimeError(f"cudaHostRegister failed: {err}")
+            self._registered = True
+            barrier()
+            if rank == 0:
+                os.unlink(path)
+
+    def ptr(self, slot: int, offset: int = 0) -> int:
+        return int(self.array.ctypes.data) + int(slot) * self.slot_bytes + int(offset)
+
+    def view(self, slot: int, shape):
+        return self.array[slot * self.slot_bytes:(slot + 1) * self.slot_bytes].reshape(shape)
+
+    def close(self):
+        if self._registered:
+            import torch
+            torch.cuda.cudart().cudaHostUnregister(self.array.ctypes.data)
+            self._registered = False
+        self.array = None
+        self._t = None
+        if self._mm is not None:
+            try:
+                self._mm.close()
+            except BufferError:
+                pass
+            self._mm = None

@@ -97,6 +97,12 @@ class Renderer:
         check(self._lib.gprt_renderer_do_raytracing_stripes_async(self._h, int(stripe_rows), int(rank), int(world), d_rgba8_ptr),
               "do_raytracing_stripes_async")
 
+    def on_render_striped_async(self, h_frame_ptr, stripe_rows, rank, world):
+        """Multi-GPU stripes with host output: this rank's rows land on their global rows of the shared (pinned / registered)
+        full-frame host buffer at h_frame_ptr."""
+        check(self._lib.gprt_renderer_on_render_stripes_async(self._h, int(stripe_rows), int(rank), int(world), h_frame_ptr),
+              "on_render_stripes_async")
+
     def set_device_transforms(self, on: bool):
         """Per-frame transforms computed on the GPU (default for scenes of >= 4096 primitives) or on the host."""
         check(self._lib.gprt_renderer_set_device_transforms(self._h, 1 if on else 0), "set_device_transforms")

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define GPRT_ABI_VERSION 1
+#define GPRT_ABI_VERSION 2
 
 /* ------------------------------------------------------------------------------------------
  * Scene / shader ABI (byte-for-byte the structs of src/ConstantBuffers.h; matrices are
@@ -125,13 +125,15 @@ typedef struct gprt_config {
     uint32_t metaballs_count;      /* METABALLS_COUNT, src/ConstantBuffers.h:12 (3 or 5)          */
     uint32_t metaball_max_steps;   /* MAX_STEPS, src/VolumetricPrimitives.hlsli:160 (128)         */
     uint32_t sdf_max_steps;        /* MaxSteps, src/SignedDistancePrimitives.hlsli:291 (512)      */
-    uint32_t math_mode;            /* GPRT_MATH_PARITY or GPRT_MATH_FAST                          */
-    uint32_t cand_per_ray;         /* candidate-queue capacity per ray slot (0 = default 4)       */
+    uint32_t math_mode;            /* GPRT_MATH_PARITY, GPRT_MATH_FMA or GPRT_MATH_FAST           */
+    uint32_t cand_per_ray;         /* candidate-queue capacity per ray slot (0 = default 2)       */
     uint32_t flags;                /* GPRT_FLAG_*                                                 */
+    uint32_t fractal_iterations;   /* FRACTAL_ITERATIONS_COUNT, src/ConstantBuffers.h:27 (4; 0 = 4, at most 8) */
 } gprt_config;
 
 enum { GPRT_MATH_PARITY = 0, /* IEEE mul/add/div/sqrt, no FMA contraction */
-       GPRT_MATH_FAST   = 1  /* FMA contraction + fast intrinsics (what DXIL `fast` allows) */ };
+       GPRT_MATH_FAST   = 1, /* FMA contraction + fast intrinsics (what DXIL `fast` allows) */
+       GPRT_MATH_FMA    = 2  /* FMA contraction only: IEEE div/sqrt, no flush-to-zero, exact transcendentals (march kernels) */ };
 enum { GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1u, /* test every AABB instead of walking the LBVH */
        GPRT_FLAG_PROFILE_KERNELS = 2u        /* CUDA events around every kernel (gprt_get_kernel_profile) */ };
 
@@ -151,7 +153,8 @@ typedef struct gprt_counters {
 enum { GPRT_K_TRAVERSE = 0, GPRT_K_INTERSECT0 = 1 /* + type id 0..9: one launch per type, only with GPRT_PER_TYPE_LAUNCHES=1 */,
        GPRT_K_RESOLVE = 11, GPRT_K_SHADE_SPAWN = 12, GPRT_K_FINAL = 13,
        GPRT_K_INTERSECT_ALL = 14 /* the production intersection kernel: all types in one persistent launch per wave */,
-       GPRT_K_COUNT = 15 };
+       GPRT_K_INTERSECT_TAIL = 15 /* the long-march continuation kernel launched after it (k_march_tail) */,
+       GPRT_K_COUNT = 16 };
 typedef struct gprt_kernel_profile {
     float    ms[GPRT_K_COUNT];
     uint32_t launches[GPRT_K_COUNT];
@@ -288,6 +291,16 @@ int gprt_dispatch_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
                              const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
                              uint32_t width, uint32_t height, gprt_rect tile,
                              void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids);
+/* Multi-GPU with HOST output: renders this rank's stripes (gprt_dispatch_stripes) and copies every row to its GLOBAL row
+ * of the caller's full-frame host buffer h_frame_rgba8 (row y at h_frame_rgba8 + y * frame_pitch_bytes), asynchronously on
+ * the context stream.  With one host frame shared by all ranks -- cudaHostAlloc(portable) in one process, or shared memory
+ * registered with cudaHostRegister in each process -- every GPU delivers its rows over its own PCIe link and nothing is
+ * gathered through one device.  gprt_sync() completes it. */
+int gprt_dispatch_stripes_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
+                                     const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
+                                     uint32_t width, uint32_t height,
+                                     uint32_t stripe_rows, uint32_t rank, uint32_t world,
+                                     void* h_frame_rgba8, size_t frame_pitch_bytes);
 /* The context's CUDA stream (cudaStream_t as void*). */
 void* gprt_get_stream(gprt_ctx* ctx);
 
@@ -295,7 +308,13 @@ void* gprt_get_stream(gprt_ctx* ctx);
 #define GPRT_HIT_TRIANGLE 0x00000000u /* | triangle instance ordinal * triangle count + PrimitiveIndex() */
 #define GPRT_HIT_AABB     0x10000000u /* | AABB instance ordinal * AABB count + GeometryIndex            */
 
+/* Waits for the context stream; returns GPRT_E_QUEUE_OVERFLOW if a queue of the last dispatch overflowed (the image is
+ * then incomplete). */
 int gprt_sync(gprt_ctx* ctx);
+/* The same check without waiting, for callers of the asynchronous device-output gprt_dispatch that synchronise their own
+ * stream: GPRT_OK while the dispatch is still running or after it finished cleanly, GPRT_E_QUEUE_OVERFLOW once it has
+ * finished with an overflow.  An unseen overflow is also returned (once) by the next gprt_dispatch* on the context. */
+int gprt_poll_status(gprt_ctx* ctx);
 int gprt_get_counters(gprt_ctx* ctx, gprt_counters* out); /* of the last dispatch; syncs */
 int gprt_last_timing(gprt_ctx* ctx, gprt_timing* out);    /* syncs                        */
 int gprt_get_kernel_profile(gprt_ctx* ctx, gprt_kernel_profile* out); /* syncs */

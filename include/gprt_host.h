@@ -66,6 +66,9 @@ int gprt_renderer_do_raytracing_stripes(gprt_renderer* r, uint32_t stripe_rows, 
 int gprt_renderer_on_render_async(gprt_renderer* r, void* h_rgba8_pinned);
 int gprt_renderer_do_raytracing_async(gprt_renderer* r, void* d_rgba8);
 int gprt_renderer_do_raytracing_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* d_rgba8);
+/* Multi-GPU with host output (gprt_dispatch_stripes_host_async): this rank's rows are copied to their global rows of
+ * h_frame_rgba8, a tightly pitched width * height * 4 host frame shared by all ranks (pinned / registered). */
+int gprt_renderer_on_render_stripes_async(gprt_renderer* r, uint32_t stripe_rows, uint32_t rank, uint32_t world, void* h_frame_rgba8);
 /* Compute the per-frame transforms on the GPU (gprt_update_transforms) instead of on the host + 128 B/primitive upload.
  * Default: on for scenes of >= 4096 primitives. */
 int gprt_renderer_set_device_transforms(gprt_renderer* r, int on);
@@ -86,6 +89,15 @@ gprt_ctx* gprt_renderer_context(gprt_renderer* r);
 /* Frame statistics in the reference's convention (calculate_frame_stats,
  * src/Renderer.cpp:375-399): million PRIMARY rays per second from the last GPU dispatch time. */
 float gprt_renderer_primary_mrays_per_s(gprt_renderer* r);
+
+/* The CUDA-free scene builder on its own (also exported by libgprt_scene.so, which links no CUDA): the arrays
+ * Renderer::initialize_scene / build_geometry / build_shader_tables assemble on the host
+ * (src/Renderer.cpp:197-356, 478-565, 732-786, 839-985) for scene_id at animation time t. */
+typedef struct gprt_scene gprt_scene;
+int gprt_scene_create(gprt_scene** out, int scene_id, uint32_t width, uint32_t height, uint32_t grid_n);
+void gprt_scene_destroy(gprt_scene* s);
+int gprt_scene_update(gprt_scene* s, float animate_geometry_time, float camera_orbit_deg, float light_orbit_deg);
+int gprt_scene_get(gprt_scene* s, gprt_scene_view* out); /* pointers stay valid until the next call on s */
 
 /* Write a tile-packed RGBA8 buffer as a binary PPM (the headless stand-in for Present). */
 int gprt_write_ppm(const char* path, const void* rgba8, uint32_t width, uint32_t height);

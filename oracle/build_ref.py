@@ -16,6 +16,7 @@ script applies to copies made in a scratch directory OUTSIDE the repository (nev
        #define MAX_RAY_RECURSION_DEPTH 3 -> g_max_recursion_depth
        const UINT MaxSteps = 512;        -> g_sdf_max_steps
        UINT MAX_STEPS = 128;             -> g_metaball_max_steps
+       #define FRACTAL_ITERATIONS_COUNT 4 -> g_fractal_iterations
      and METABALLS_COUNT is set to 3 or 5 per variant (the reference ships both code paths,
      src/ConstantBuffers.h:12-25, src/VolumetricPrimitives.hlsli:91-111)
   8. two counting hooks (one line each): SDF distance evaluations and metaball march steps.
@@ -68,6 +69,7 @@ def rewrite_file(name: str, text: str, metaballs: int) -> str:
         if name == "ConstantBuffers.h":
             code = re.sub(r"#define\s+MAX_RAY_RECURSION_DEPTH\s+\d+", "#define MAX_RAY_RECURSION_DEPTH g_max_recursion_depth", code)
             code = re.sub(r"#define\s+METABALLS_COUNT\s+\d+", f"#define METABALLS_COUNT {metaballs}", code)
+            code = re.sub(r"#define\s+FRACTAL_ITERATIONS_COUNT\s+\d+", "#define FRACTAL_ITERATIONS_COUNT ((int)g_fractal_iterations)", code)
         if name == "SignedDistancePrimitives.hlsli":
             code = re.sub(r"const\s+UINT\s+MaxSteps\s*=\s*512\s*;", "const UINT MaxSteps = g_sdf_max_steps;", code)
         if name == "VolumetricPrimitives.hlsli":
@@ -85,7 +87,7 @@ def rewrite_file(name: str, text: str, metaballs: int) -> str:
 
 def check_rewrites(scratch: str):
     blob = "".join(open(os.path.join(scratch, f)).read() for f in FILES)
-    for needle in ("g_max_recursion_depth", "g_sdf_max_steps", "g_metaball_max_steps", "ORACLE_COUNT_MB_STEP", "ORACLE_COUNT_SDF"):
+    for needle in ("g_max_recursion_depth", "g_sdf_max_steps", "g_metaball_max_steps", "g_fractal_iterations", "ORACLE_COUNT_MB_STEP", "ORACLE_COUNT_SDF"):
         assert needle in blob, f"rewrite for {needle} did not apply (reference changed?)"
 
 

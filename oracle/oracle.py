@@ -20,7 +20,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 class OracleConfig(C.Structure):
     _fields_ = [("max_recursion_depth", C.c_uint32), ("sdf_max_steps", C.c_uint32), ("metaball_max_steps", C.c_uint32),
-                ("force_brute_force", C.c_uint32)]
+                ("force_brute_force", C.c_uint32), ("fractal_iterations", C.c_uint32)]
 
 
 class OracleCounters(C.Structure):
@@ -56,6 +56,8 @@ class Oracle:
         L.oracle_intersect_local.argtypes = [u32, u32, vp, vp, f32, f32, u32, f32, f32, C.POINTER(f32), vp]
         L.oracle_sdf_distance.restype = f32
         L.oracle_sdf_distance.argtypes = [u32, vp]
+        L.oracle_set_fractal_iterations.restype = None
+        L.oracle_set_fractal_iterations.argtypes = [u32]
         L.oracle_checkers_box_filter.restype = f32
         L.oracle_checkers_box_filter.argtypes = [vp, vp, vp, u32]
         L.oracle_fresnel_schlick.restype = None
@@ -67,6 +69,7 @@ class Oracle:
         L.oracle_metaballs_count.restype = C.c_int
         L.oracle_kind.restype = C.c_char_p
         L.oracle_max_threads.restype = C.c_int
+        L.oracle_last_threads.restype = C.c_int
         self.L = L
         self.kind = L.oracle_kind().decode()
         self.metaballs = L.oracle_metaballs_count()
@@ -75,12 +78,18 @@ class Oracle:
     def max_threads(self):
         return int(self.L.oracle_max_threads())
 
-    def set_scene(self, scene, force_brute_force=False, max_recursion_depth=None, sdf_max_steps=None, metaball_max_steps=None):
+    def last_threads(self):
+        """Threads the last render() really ran on."""
+        return int(self.L.oracle_last_threads())
+
+    def set_scene(self, scene, force_brute_force=False, max_recursion_depth=None, sdf_max_steps=None, metaball_max_steps=None,
+                  fractal_iterations=None):
         """scene: gpuraytracer_b200.SceneData (numpy arrays with the ABI layouts)."""
         cfg = OracleConfig(max_recursion_depth if max_recursion_depth is not None else scene.config.max_recursion_depth,
                            sdf_max_steps if sdf_max_steps is not None else scene.config.sdf_max_steps,
                            metaball_max_steps if metaball_max_steps is not None else scene.config.metaball_max_steps,
-                           1 if force_brute_force else 0)
+                           1 if force_brute_force else 0,
+                           fractal_iterations if fractal_iterations is not None else getattr(scene.config, "fractal_iterations", 4))
         if scene.config.metaballs_count != self.metaballs:
             raise ValueError(f"oracle built for {self.metaballs} metaballs, scene wants {scene.config.metaballs_count}")
         a = {k: np.ascontiguousarray(getattr(scene, k)) for k in ("aabbs", "vertices", "indices", "instances", "hit_groups")}
@@ -117,6 +126,9 @@ class Oracle:
         hit = self.L.oracle_intersect_local(hit_group_kind, primitive_type, o.ctypes.data, d.ctypes.data, tmin, tcurrent, ray_flags,
                                             elapsed_time, step_scale, C.byref(t), n.ctypes.data)
         return (bool(hit), float(t.value), n)
+
+    def set_fractal_iterations(self, n):
+        self.L.oracle_set_fractal_iterations(int(n))
 
     def sdf_distance(self, primitive_type, p):
         p = np.asarray(p, np.float32)

@@ -53,6 +53,8 @@ namespace hlsl {
 static uint g_max_recursion_depth = 3;
 static uint g_sdf_max_steps = 512;
 static uint g_metaball_max_steps = 128;
+static int g_last_threads = 1;
+static uint g_fractal_iterations = 4; // FRACTAL_ITERATIONS_COUNT, src/ConstantBuffers.h:27
 
 // ---------------------------------------------------------------------------------------------
 // Work counters (thread-local, summed after a render).
@@ -440,6 +442,7 @@ extern "C" {
 
 struct oracle_config {
     uint32_t max_recursion_depth, sdf_max_steps, metaball_max_steps, force_brute_force;
+    uint32_t fractal_iterations; // 0 = the reference's 4
 };
 struct oracle_counters {
     uint64_t radiance_rays, shadow_rays, isect[3], sdf_evals[8], metaball_steps, aabb_tests;
@@ -476,6 +479,7 @@ int oracle_set_scene(const gprt_aabb* aabbs, uint32_t n_aabbs, const gprt_vertex
         g_max_recursion_depth = cfg->max_recursion_depth;
         g_sdf_max_steps = cfg->sdf_max_steps;
         g_metaball_max_steps = cfg->metaball_max_steps;
+        g_fractal_iterations = cfg->fractal_iterations ? cfg->fractal_iterations : 4u;
     }
     g_sc.use_bvh = n_aabbs > 64 && !(cfg && cfg->force_brute_force);
     if (g_sc.use_bvh) {
@@ -510,6 +514,10 @@ int oracle_render(const gprt_scene_cb* scene, const gprt_prim_per_frame* per_fra
 #endif
 #pragma omp parallel num_threads(n_threads)
     {
+#ifdef _OPENMP
+#pragma omp single
+        g_last_threads = omp_get_num_threads();
+#endif
         tl_counters = Counters();
         std::vector<float4> row(tile.w);
 #pragma omp for schedule(dynamic, 1)
@@ -541,6 +549,9 @@ int oracle_render(const gprt_scene_cb* scene, const gprt_prim_per_frame* per_fra
     }
     return 0;
 }
+
+// threads the last oracle_render really ran on (omp_get_num_threads inside its parallel region)
+int oracle_last_threads(void) { return hlsl::g_last_threads; }
 
 int oracle_max_threads(void) {
 #ifdef _OPENMP
@@ -574,6 +585,9 @@ int oracle_intersect_local(uint32_t hit_group_kind, uint32_t primitive_type, con
     if (hit) { *thit_out = thit; normal_out[0] = attr.normal.x; normal_out[1] = attr.normal.y; normal_out[2] = attr.normal.z; }
     return hit ? 1 : 0;
 }
+// FRACTAL_ITERATIONS_COUNT for the function-level probes below (oracle_set_scene sets it for renders)
+void oracle_set_fractal_iterations(uint32_t n) { hlsl::g_fractal_iterations = n ? n : 4u; }
+
 float oracle_sdf_distance(uint32_t primitive_type, const float* p) {
     return hlsl::GetDistanceFromSignedDistancePrimitive(hlsl::float3(p[0], p[1], p[2]), (hlsl::SignedDistancePrimitive::Enum)primitive_type);
 }

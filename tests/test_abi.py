@@ -27,7 +27,7 @@ def test_struct_sizes_match_reference_layout():
     assert _capi.HIT_GROUP_DTYPE.itemsize == 96
     assert _capi.HIT_GROUP_DTYPE.fields["material_cb"][1] == 32
     assert _capi.HIT_GROUP_DTYPE.fields["instance_index"][1] == 80
-    assert C.sizeof(_capi.Config) == 32
+    assert C.sizeof(_capi.Config) == 36
     assert C.sizeof(_capi.Rect) == 16
 
 
@@ -53,9 +53,9 @@ def test_library_exports_every_declared_symbol():
 
 def test_default_config_is_the_reference_compile_time_values():
     cfg = default_config()
-    assert (cfg.abi_version, cfg.max_recursion_depth, cfg.metaballs_count) == (1, 3, 3)
+    assert (cfg.abi_version, cfg.max_recursion_depth, cfg.metaballs_count) == (2, 3, 3)
     assert (cfg.metaball_max_steps, cfg.sdf_max_steps) == (128, 512)
-    assert _capi.lib().gprt_abi_version() == 1
+    assert _capi.lib().gprt_abi_version() == 2
 
 
 def test_error_strings():

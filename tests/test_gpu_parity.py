@@ -188,6 +188,47 @@ def test_two_level_instancing_with_many_instances_and_spill_rounds(monkeypatch):
     assert len(np.unique(boxes // n)) >= 10
 
 
+def test_queue_overflow_is_reported_on_every_path():
+    """Candidate queues too small for the scene (cand_per_ray = 1 on the stacked 41-instance scene): the synchronous
+    call returns GPRT_E_QUEUE_OVERFLOW, and so does the asynchronous device-output path to a caller who synchronises
+    the stream itself -- through gprt_poll_status and, if unseen, through the next dispatch."""
+    import ctypes as C
+    import torch
+    lib = _capi.lib()
+    r = Renderer(scene_id=5, width=480, height=270, grid_n=64, device=None)
+    r.on_update(1.0)
+    s = r.scene()
+    inst = np.zeros(41, dtype=s.instances.dtype)
+    inst[0] = s.instances[0]
+    for k in range(40):
+        inst[1 + k] = s.instances[1]
+        inst[1 + k]["transform"][1, 3] += 6.0 * (k % 5)
+        inst[1 + k]["transform"][0, 3] += 3.0 * (k // 5)
+    h = C.c_void_p()
+    cfg = make_cfg()
+    cfg.max_recursion_depth, cfg.metaballs_count = s.config.max_recursion_depth, s.config.metaballs_count
+    cfg.metaball_max_steps, cfg.sdf_max_steps = s.config.metaball_max_steps, s.config.sdf_max_steps
+    cfg.cand_per_ray = 1
+    assert lib.gprt_create(C.byref(h), 0, C.byref(cfg)) == 0
+    try:
+        assert lib.gprt_set_geometry(h, s.aabbs.ctypes.data, len(s.aabbs), s.vertices.ctypes.data, len(s.vertices), s.indices.ctypes.data,
+                                     len(s.indices), inst.ctypes.data, len(inst)) == 0
+        assert lib.gprt_set_hit_group_table(h, s.hit_groups.ctypes.data, len(s.hit_groups), s.hit_groups.dtype.itemsize) == 0
+        assert lib.gprt_build_accel(h) == 0
+        img = np.zeros((270, 480, 4), np.uint8)
+        args = (s.scene_cb.ctypes.data, s.per_frame.ctypes.data, len(s.per_frame), 480, 270, _capi.Rect(0, 0, 480, 270))
+        assert lib.gprt_dispatch_host(h, *args, img.ctypes.data, 480 * 4, None) == _capi.GPRT_E_QUEUE_OVERFLOW
+        d_img = torch.zeros((270, 480, 4), dtype=torch.uint8, device="cuda")
+        assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == 0   # asynchronous: nothing known yet
+        torch.cuda.synchronize()                                                          # the caller's own synchronisation
+        assert lib.gprt_poll_status(h) == _capi.GPRT_E_QUEUE_OVERFLOW
+        assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == _capi.GPRT_E_QUEUE_OVERFLOW  # unseen overflow, reported once
+        assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == 0
+        assert lib.gprt_sync(h) == _capi.GPRT_E_QUEUE_OVERFLOW
+    finally:
+        lib.gprt_destroy(h)
+
+
 def test_config5_lbvh_equals_brute_force_and_oracle():
     """LBVH traversal must produce exactly the brute-force candidate set (bit-identical images)."""
     a_img, a_ids, scene, a_c, _ = gpu_render(5, 480, 270, 1.0, grid_n=32)
@@ -329,13 +370,22 @@ def test_device_side_transform_update_is_bit_identical():
         assert r.device_transforms().tobytes() == r.scene().per_frame.tobytes()
 
 
-def test_internal_banding_is_invisible():
-    """A frame larger than the internal pass size is rendered in bands; compare against tiles."""
-    with Renderer(scene_id=0, width=2560, height=1800, device=0, config=make_cfg()) as r:  # 4.6 Mpx > 2^22
+def test_internal_banding_is_invisible(monkeypatch):
+    """A frame larger than the internal pass size is rendered in row bands (the pass size follows the free device
+    memory; GPRT_PASS_PIXELS forces a small one here); compare against one pass and against tiles."""
+    with Renderer(scene_id=0, width=1280, height=900, device=0, config=make_cfg()) as r:
+        r.on_init()
+        one_pass, _ = r.on_render()
+        one_pass = one_pass.copy()
+        assert r.launch_count() <= 16  # three waves in a single pass
+    monkeypatch.setenv("GPRT_PASS_PIXELS", str(1 << 18))  # 1.15 Mpx frame -> 5 bands
+    with Renderer(scene_id=0, width=1280, height=900, device=0, config=make_cfg()) as r:
         r.on_init()
         full, _ = r.on_render()
-        tile, _ = r.on_render(tile=(1000, 1500, 400, 200))
-        np.testing.assert_array_equal(tile, full[1500:1700, 1000:1400])
+        assert r.launch_count() > 4 * 12
+        tile, _ = r.on_render(tile=(500, 700, 400, 200))
+        np.testing.assert_array_equal(tile, full[700:900, 500:900])
+        np.testing.assert_array_equal(full, one_pass)
 
 
 def test_device_output_and_optional_buffers():
@@ -443,16 +493,57 @@ def test_empty_and_degenerate_scenes():
     assert (np.abs(img.astype(int) - g["rgba8"].astype(int)).max(-1) > 2).sum() <= 3
 
 
-def test_refit_accel_matches_rebuild():
+def _render_low_level(s, aabbs, w, h, flags=0, refit_to=None):
+    """gprt_create / set_geometry / set_hit_group_table / build_accel [/ refit_accel] / dispatch_host on scene `s` with the
+    given AABBs; returns (rgba8, hit ids)."""
     import ctypes as C
     lib = _capi.lib()
-    with Renderer(scene_id=5, width=320, height=180, grid_n=16, device=0, config=make_cfg()) as r:
-        r.on_init()
+    hnd = C.c_void_p()
+    cfg = default_config()
+    cfg.flags = flags
+    cfg.max_recursion_depth = s.config.max_recursion_depth
+    assert lib.gprt_create(C.byref(hnd), 0, C.byref(cfg)) == 0
+    try:
+        aabbs = np.ascontiguousarray(aabbs)
+        assert lib.gprt_set_geometry(hnd, aabbs.ctypes.data, len(aabbs), s.vertices.ctypes.data, len(s.vertices), s.indices.ctypes.data,
+                                     len(s.indices), s.instances.ctypes.data, len(s.instances)) == 0
+        assert lib.gprt_set_hit_group_table(hnd, s.hit_groups.ctypes.data, len(s.hit_groups), 96) == 0
+        assert lib.gprt_build_accel(hnd) == 0
+        if refit_to is not None:
+            refit_to = np.ascontiguousarray(refit_to)
+            assert lib.gprt_refit_accel(hnd, refit_to.ctypes.data, len(refit_to)) == 0
+        img = np.zeros((h, w, 4), np.uint8)
+        ids = np.zeros((h, w), np.uint32)
+        assert lib.gprt_dispatch_host(hnd, s.scene_cb.ctypes.data, s.per_frame.ctypes.data, len(s.per_frame), w, h, _capi.Rect(0, 0, w, h),
+                                      img.ctypes.data, w * 4, ids.ctypes.data) == 0
+        return img, ids
+    finally:
+        lib.gprt_destroy(hnd)
+
+
+def test_refit_accel_matches_rebuild():
+    """gprt_refit_accel with boxes that really moved: a third of the boxes shifted, a third grown, against a fresh
+    build over the moved boxes, the brute-force loop and the oracle (the primitives keep their transforms, so what
+    changes is along which rays each one is visible: a primitive is tested exactly where its AABB is hit)."""
+    from dataclasses import replace
+    W, H = 320, 180
+    with Renderer(scene_id=5, width=W, height=H, grid_n=24, device=None) as r:
+        r.on_update(1.0)
         s = r.scene()
-        moved = s.aabbs.copy()
-        moved["min"][:, 1] += 0.0  # same boxes: refit must reproduce the image exactly
-        a, _ = r.on_render()
-        a = a.copy()
-        assert lib.gprt_refit_accel(r.context, moved.ctypes.data, len(moved)) == 0
-        b, _ = r.on_render()
-        np.testing.assert_array_equal(a, b)
+    moved = s.aabbs.copy()
+    idx = np.arange(len(moved))
+    moved["min"][idx % 3 == 0, 0] += 0.75   # shifted in x
+    moved["max"][idx % 3 == 0, 0] += 0.75
+    moved["min"][idx % 3 == 1] -= 0.5       # grown
+    moved["max"][idx % 3 == 1] += 0.5
+    refit_img, refit_ids = _render_low_level(s, s.aabbs, W, H, refit_to=moved)
+    built_img, built_ids = _render_low_level(s, moved, W, H)
+    brute_img, brute_ids = _render_low_level(s, moved, W, H, flags=GPRT_FLAG_BRUTE_FORCE_TRAVERSAL)
+    np.testing.assert_array_equal(refit_img, brute_img)
+    np.testing.assert_array_equal(refit_ids, brute_ids)
+    np.testing.assert_array_equal(built_img, brute_img)
+    np.testing.assert_array_equal(built_ids, brute_ids)
+    orig_img, _ = _render_low_level(s, s.aabbs, W, H)
+    assert (orig_img != refit_img).any()    # the move is visible
+    ref = oracle_render(replace(s, aabbs=moved))
+    check(ref, refit_img, refit_ids)
