@@ -464,8 +464,7 @@ def run_gpu(args):
 
 
 def roofline(args, conf, device, world, m):
-    """The dominant kernel of the step is the intersection kernel (all primitive types in one persistent launch per wave, plus
-    its long-march continuation launch).  Its launches are timed live with CUDA events on the launching stream
+    """The dominant kernel of the step is the intersection kernel (all primitive types in one persistent launch per wave).  Its launches are timed live with CUDA events on the launching stream
     (GPRT_FLAG_PROFILE_KERNELS) over full single-GPU frames of the same workload, L2 flushed between frames; achieved =
     algorithmic FP32 work of those launches (device work counters x the hand-counted flops per unit of DESIGN.md section 5) /
     their duration, against the FP32-FMA issue-rate peak measured in this run.  `frac_of_timed_step` divides the same work by
@@ -473,7 +472,7 @@ def roofline(args, conf, device, world, m):
     does the same for the most memory-bound kernel (the final fold) against the measured HBM copy bandwidth."""
     import torch
     from gpuraytracer_b200 import GPRT_MATH_FAST, GPRT_MATH_FMA, GPRT_MATH_PARITY, Renderer, default_config
-    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, GPRT_K_INTERSECT_TAIL, KERNEL_NAMES
+    from gpuraytracer_b200._capi import GPRT_FLAG_PROFILE_KERNELS, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, KERNEL_NAMES
     cfg = default_config()
     cfg.math_mode = {"parity": GPRT_MATH_PARITY, "fma": GPRT_MATH_FMA, "fast": GPRT_MATH_FAST}[args.math]
     cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = cfg.fractal_iterations = 0
@@ -508,7 +507,7 @@ def roofline(args, conf, device, world, m):
     launches = [n // reps for n in launches]
     kernel_ms = {KERNEL_NAMES[k]: round(ms[k], 4) for k in range(nk) if launches[k]}
     flops = sum(work[t] * FLOPS_PER_UNIT[t] for t in range(10))
-    isect_ms = ms[GPRT_K_INTERSECT_ALL] + ms[GPRT_K_INTERSECT_TAIL]
+    isect_ms = ms[GPRT_K_INTERSECT_ALL]
     dur = isect_ms * 1e-3
     n_l = max(launches[GPRT_K_INTERSECT_ALL], 1)
     peaks = {}
@@ -522,11 +521,11 @@ def roofline(args, conf, device, world, m):
         fp32_peak, peak_src = 74.4, "nominal fallback: 148 SMs x 128 lanes x 2 x 1.965 GHz"
     # DRAM traffic per launch of the same kernel: NOT measured in this run (no profiler here) -- read from the committed ncu --set full
     # capture of the same workload under profiles/ (mean over the launches of one frame); null when none is committed
-    traffic, traffic_src = _committed_traffic(conf, ("r02_ncu_full_k_intersect.json", "r01_ncu_full_k_intersect_coop.json"))
+    traffic, traffic_src = _committed_traffic(conf, ("r02_ncu_full_k_intersect_coop.json", "r01_ncu_full_k_intersect_coop.json"))
     plan = plan_for(args.config, world, args)
     # FP32 rate of the whole timed pipeline per GPU: the step's frames x flops per frame / the step's time / N GPUs
     pipeline_tflops = flops * plan["frames_per_step"] / (m["ms_per_step"] * 1e-3) / 1e12 / world if m["ms_per_step"] else None
-    roof = {"bound": "fp32", "kernel": "k_intersect (all primitive types, one persistent launch per wave) + k_march_tail (its long-march continuation)",
+    roof = {"bound": "fp32", "kernel": "k_intersect_coop (all primitive types, one persistent launch per wave)",
             "achieved": round(achieved, 3), "peak": round(fp32_peak, 2), "unit": "TFLOP/s",
             "frac": round(achieved / fp32_peak, 4),
             "frac_of_timed_step": round(pipeline_tflops / fp32_peak, 4) if pipeline_tflops else None,

@@ -15,8 +15,7 @@ GPRT_ABI_VERSION = 2
 GPRT_MATH_PARITY, GPRT_MATH_FAST, GPRT_MATH_FMA = 0, 1, 2
 GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1
 GPRT_FLAG_PROFILE_KERNELS = 2
-GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL = 0, 1, 11, 12, 13, 14
-GPRT_K_INTERSECT_TAIL, GPRT_K_COUNT = 15, 16
+GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14, 15
 GPRT_HIT_MISS = 0xFFFFFFFF
 GPRT_HIT_TRIANGLE = 0x00000000
 GPRT_HIT_AABB = 0x10000000
@@ -43,7 +42,7 @@ class Counters(C.Structure):
 
 
 class KernelProfile(C.Structure):
-    _fields_ = [("ms", C.c_float * 16), ("launches", C.c_uint32 * 16), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
+    _fields_ = [("ms", C.c_float * 15), ("launches", C.c_uint32 * 15), ("work", C.c_uint64 * 10), ("candidates", C.c_uint64 * 10)]
 
 
 class WaveStats(C.Structure):
@@ -68,7 +67,7 @@ class SceneView(C.Structure):
 
 # numpy views of the ABI structs (sizes asserted against include/gprt.h in tests/test_abi.py)
 KERNEL_NAMES = ["traverse", "isect_box", "isect_spheres", "isect_metaballs", "isect_minispheres", "isect_roundcube", "isect_sqtorus",
-                "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final", "intersect_all", "intersect_tail"]
+                "isect_twtorus", "isect_cog", "isect_cylinder", "isect_pyramid", "resolve", "shade_spawn", "final", "intersect_all"]
 TYPE_NAMES = KERNEL_NAMES[1:11]
 
 SCENE_CB_DTYPE = np.dtype([("projection_to_world", "<f4", (4, 4)), ("camera_position", "<f4", 4), ("light_position", "<f4", 4),

@@ -16,6 +16,7 @@ namespace {
 
 constexpr int kBlock = 256;
 constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kRefillMin = 8; // idle lanes of a warp that trigger a refill from the queue (measured: 1, 8, 16, 24 within 3 %)
 
 __device__ __forceinline__ unsigned long long pack_key(float t, uint32_t code) {
     // t >= 0 here, so the IEEE bit pattern orders like the value; fabsf folds -0 into +0
@@ -575,6 +576,7 @@ __global__ void __launch_bounds__(kBlock, 5) k_final_color(const __grid_constant
 
 #include "march.cuh" // queue plumbing, analytic tests (same anonymous namespace)
 #include "march_coop.cuh" // k_intersect_coop: warp-cooperative sphere tracer (the production path)
+#include "march_lane.cuh" // k_intersect_lane: per-lane sphere tracer (measured alternative, GPRT_ISECT_VARIANT=2)
 
 namespace gprt {
 namespace {
@@ -623,15 +625,21 @@ int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers&
     return launch_traverse_t<false>(sc, pp, wb, wave, (cudaStream_t)stream);
 }
 
-// GPRT_ISECT_VARIANT=-1 (profiling aid): with GPRT_PER_TYPE_LAUNCHES=1, run the one-candidate-per-thread kernels, which
-// also fill the per-candidate cost statistics of gprt_get_wave_stats.  Otherwise: the production kernels.
-bool stats_kernels() {
+// GPRT_ISECT_VARIANT: 0 (default) the warp-cooperative k_intersect_coop; 2 the per-lane k_intersect_lane (A/B, march_lane.cuh);
+// -1 (profiling aid, with GPRT_PER_TYPE_LAUNCHES=1) the one-candidate-per-thread kernels, which also fill the per-candidate
+// cost statistics of gprt_get_wave_stats.
+int isect_variant() {
     static int v = -1000;
     if (v == -1000) { const char* e = getenv("GPRT_ISECT_VARIANT"); v = e ? atoi(e) : 0; }
-    return v == -1;
+    return v;
 }
-
-constexpr int kRefillMin = 8; // idle lanes of a warp that trigger a refill from the queue (measured: 1, 8, 16, 24 within 3 %)
+bool stats_kernels() { return isect_variant() == -1; }
+// GPRT_ISECT_BLOCKS (tuning aid): resident blocks per SM of the persistent intersection kernel (default: what fits, 4)
+int isect_blocks_limit() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("GPRT_ISECT_BLOCKS"); v = e ? atoi(e) : 0; }
+    return v;
+}
 
 template <class K> int persistent_grid(K kernel) {
     int per_sm = 0;
@@ -686,12 +694,26 @@ template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, c
     static const int grid = persistent_grid(k_intersect_coop<NB, kRefillMin>);
     k_intersect_coop<NB, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
+template <int NB> void launch_lane_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
+    static const int per_sm = [] {
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_intersect_lane<NB>, kBlock, 0);
+        if (n < 1) n = 1;
+        const int lim = isect_blocks_limit();
+        return (lim > 0 && lim < n) ? lim : n;
+    }();
+    k_intersect_lane<NB><<<sm_count() * per_sm, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
+}
 int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {
+    if (isect_variant() == 2) {
+        if (metaballs == 5) launch_lane_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+        else launch_lane_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+        return 1;
+    }
     if (metaballs == 5) launch_coop_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
     else launch_coop_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
     return 1;
 }
-
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
     k_resolve<<<sm_count() * 4, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
     return 1;

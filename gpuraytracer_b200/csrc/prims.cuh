@@ -302,13 +302,10 @@ GPRT_HD V3 fractal_fold(V3 p, float a, float hz) {
 // `iters` = FRACTAL_ITERATIONS_COUNT (src/ConstantBuffers.h:27; 4 in the reference, a run-time knob here, <= 8).
 GPRT_HD float sd_fractal_pyramid(V3 p, V3 h, uint32_t iters) {
     const float a = h.z * h.y / h.x;
-    if (iters == 4u) { // the reference's value: fully unrolled
-#pragma unroll
-        for (int n = 0; n < 4; n++) p = fractal_fold(p, a, h.z);
-    } else {
+    // Not unrolled: the folds are one dependent chain anyway, and the march kernels hold this body once per SDF type --
+    // ncu showed their warps starved for instructions (stall_no_instruction 6 per issue) with 215 KB of unrolled code.
 #pragma unroll 1
-        for (uint32_t n = 0; n < iters; n++) p = fractal_fold(p, a, h.z);
-    }
+    for (uint32_t n = 0; n < iters; n++) p = fractal_fold(p, a, h.z);
     // pow(Scale, -n) = exp2(log2(2) * -n) = 2^-n exactly
 #if defined(__CUDA_ARCH__)
     const float inv_scale = __uint_as_float((127u - iters) << 23);

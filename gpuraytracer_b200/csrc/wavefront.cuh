@@ -128,6 +128,7 @@ struct WaveBuffers {
     WaveCtrl* ctrl;    // [kMaxDepth + 1]
     uint2* spill[2];   // traversal hand-over queues (ray slot, subtree root), ping-pong by round
     uint32_t spill_capacity;
+
     // per-level, per-pixel hit records: index (level - 1) * n_pixels + pixel
     float4* lvl_o_t;   // ray origin xyz, committed t
     float4* lvl_d;     // ray direction xyz

@@ -153,8 +153,7 @@ typedef struct gprt_counters {
 enum { GPRT_K_TRAVERSE = 0, GPRT_K_INTERSECT0 = 1 /* + type id 0..9: one launch per type, only with GPRT_PER_TYPE_LAUNCHES=1 */,
        GPRT_K_RESOLVE = 11, GPRT_K_SHADE_SPAWN = 12, GPRT_K_FINAL = 13,
        GPRT_K_INTERSECT_ALL = 14 /* the production intersection kernel: all types in one persistent launch per wave */,
-       GPRT_K_INTERSECT_TAIL = 15 /* the long-march continuation kernel launched after it (k_march_tail) */,
-       GPRT_K_COUNT = 16 };
+       GPRT_K_COUNT = 15 };
 typedef struct gprt_kernel_profile {
     float    ms[GPRT_K_COUNT];
     uint32_t launches[GPRT_K_COUNT];

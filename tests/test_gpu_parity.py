@@ -222,6 +222,8 @@ def test_queue_overflow_is_reported_on_every_path():
         assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == 0   # asynchronous: nothing known yet
         torch.cuda.synchronize()                                                          # the caller's own synchronisation
         assert lib.gprt_poll_status(h) == _capi.GPRT_E_QUEUE_OVERFLOW
+        assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == 0   # the previous overflow has been seen
+        torch.cuda.synchronize()                                                          # ... this one is not looked at
         assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == _capi.GPRT_E_QUEUE_OVERFLOW  # unseen overflow, reported once
         assert lib.gprt_dispatch(h, *args, d_img.data_ptr(), 480 * 4, None, None) == 0
         assert lib.gprt_sync(h) == _capi.GPRT_E_QUEUE_OVERFLOW

@@ -56,7 +56,7 @@ def main():
             out["build_ms"] = r.timing().build_accel_ms
             if flags:
                 p = r.kernel_profile()
-                out["kernel_ms"] = {KNAMES[i]: round(p.ms[i], 4) for i in range(15) if p.launches[i]}
+                out["kernel_ms"] = {KNAMES[i]: round(p.ms[i], 4) for i in range(len(KNAMES)) if p.launches[i]}
                 out["work"] = {KNAMES[1 + t]: int(p.work[t]) for t in range(10) if p.candidates[t]}
                 out["candidates"] = {KNAMES[1 + t]: int(p.candidates[t]) for t in range(10) if p.candidates[t]}
                 out["fp32_peak_tflops"] = round(r.measure_fp32_peak(), 2)

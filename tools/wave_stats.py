@@ -10,8 +10,9 @@ import json
 import os
 import sys
 
-os.environ.setdefault("GPRT_ISECT_VARIANT", "-1")
-os.environ.setdefault("GPRT_PER_TYPE_LAUNCHES", "1")
+if "--production" not in sys.argv:  # default: the one-candidate-per-thread statistics kernels; --production: the shipped kernels (tail counts)
+    os.environ.setdefault("GPRT_ISECT_VARIANT", "-1")
+    os.environ.setdefault("GPRT_PER_TYPE_LAUNCHES", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 from gpuraytracer_b200 import Renderer, default_config  # noqa: E402
@@ -25,6 +26,7 @@ def main():
     ap.add_argument("--scene", type=int, default=2)
     ap.add_argument("--fast", action="store_true")
     ap.add_argument("--time", type=float, default=0.0)
+    ap.add_argument("--production", action="store_true")
     a = ap.parse_args()
     cfg = default_config()
     cfg.math_mode = 1 if a.fast else 0
