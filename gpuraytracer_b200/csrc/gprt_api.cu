@@ -27,7 +27,7 @@ constexpr uint32_t kMaxPassPixelsSingle = (1u << 26) - 1u; // 26-bit pixel field
 constexpr uint32_t kMaxPassPixelsMulti = 1u << 22;         // multi-instance spill entries pack the ray slot in kSpillRayBits
 constexpr int kStagingSlots = 3;                  // == frame_count of the reference (src/Renderer.h:92)
 constexpr int kMaxBands = 256;
-constexpr uint32_t kSpillBudget = 64;     // LBVH node fetches one thread spends on a ray before handing the rest of the walk on
+constexpr uint32_t kSpillBudget = 32;     // wide-node fetches one thread spends on a ray before handing the rest of the walk on (measured: 24..48 within 2 %, 128 +6 %)
 constexpr uint32_t kSpillMinPrims = 4096; // below this no ray walks long enough to matter and the spill rounds are not launched
 
 struct HostCtrlCopy { WaveCtrl ctrl[kMaxDepth + 2]; };
@@ -68,7 +68,11 @@ struct gprt_ctx {
     InstDev* d_tri_insts = nullptr;
     InstDev* d_aabb_insts = nullptr;
     Material* d_plane_mats = nullptr;
-    float4* d_nodes = nullptr;
+    float4* d_nodes = nullptr;         // binary LBVH (build / refit)
+    float4* d_wide = nullptr;          // its 4-wide collapse: what the walk reads
+    float4* d_top = nullptr;           // the top of the wide tree, breadth first (staged in shared memory by the walk)
+    uint32_t* d_n_top = nullptr;
+    uint32_t top_capacity = 288;       // nodes of the staged top array (36 KB; GPRT_TOP_NODES)
     uint32_t* d_sorted = nullptr;
     void* d_lbvh_scratch = nullptr;
     SceneDev scene;
@@ -288,7 +292,8 @@ int upload_static_scene(gprt_ctx* c) {
 
     cudaStreamSynchronize(c->stream);
     cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
-    cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch);
+    cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_wide); cudaFree(c->d_top); cudaFree(c->d_n_top);
+    c->d_wide = c->d_top = nullptr; c->d_n_top = nullptr;
     cudaFree(c->d_tri_insts); cudaFree(c->d_aabb_insts); cudaFree(c->d_plane_mats);
     c->d_aabbs = nullptr; c->d_prims = nullptr; c->d_prim_types = nullptr; c->d_tri_pos = c->d_tri_nrm = nullptr; c->d_nodes = nullptr; c->d_sorted = nullptr; c->d_lbvh_scratch = nullptr;
     c->d_tri_insts = c->d_aabb_insts = nullptr; c->d_plane_mats = nullptr;
@@ -300,6 +305,9 @@ int upload_static_scene(gprt_ctx* c) {
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_pos, (tri_pos.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_nrm, (tri_nrm.size() + 1) * sizeof(float)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_nodes, (size_t)(n ? n : 1) * 4 * sizeof(float4)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_wide, (size_t)(n ? n : 1) * 8 * sizeof(float4)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_top, (size_t)c->top_capacity * 8 * sizeof(float4)));
+    GPRT_CUDA(c, cudaMalloc((void**)&c->d_n_top, sizeof(uint32_t)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_sorted, (size_t)(n ? n : 1) * sizeof(uint32_t)));
     GPRT_CUDA(c, cudaMalloc(&c->d_lbvh_scratch, lbvh_scratch_bytes(n ? n : 1)));
     GPRT_CUDA(c, cudaMalloc((void**)&c->d_tri_insts, tri_insts.size() * sizeof(InstDev)));
@@ -322,6 +330,9 @@ int upload_static_scene(gprt_ctx* c) {
     SceneDev& s = c->scene;
     std::memset(&s, 0, sizeof s);
     s.bvh_nodes = c->d_nodes;
+    s.wide_nodes = c->d_wide;
+    s.top_nodes = c->d_top;
+    s.n_top = 0;
     s.n_prims = n;
     s.aabbs = c->d_aabbs;
     s.prims = c->d_prims;
@@ -472,6 +483,7 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : (c0.math_mode == GPRT_MATH_FMA) ? kernels_fma() : kernels_parity();
     { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
     { const char* e = getenv("GPRT_SPILL_BUDGET"); c->spill_budget = e ? (uint32_t)atoi(e) : kSpillBudget; } // tuning aid
+    { const char* e = getenv("GPRT_TOP_NODES"); if (e && atoi(e) > 0) c->top_capacity = (uint32_t)atoi(e) > 1400u ? 1400u : (uint32_t)atoi(e); }
     { const char* e = getenv("GPRT_PASS_PIXELS"); c->pass_pixel_override = e ? (uint32_t)atoll(e) : 0u; }
     { const char* e = getenv("GPRT_SPILL_CAPACITY"); c->spill_capacity_limit = e ? (uint32_t)atoi(e) : 0u; }
     std::memset(&c->scene, 0, sizeof c->scene);
@@ -497,6 +509,7 @@ void gprt_destroy(gprt_ctx* c) {
     cudaFree(c->d_tri_insts); cudaFree(c->d_aabb_insts); cudaFree(c->d_plane_mats);
     cudaFree(c->d_aabbs); cudaFree(c->d_prims); cudaFree(c->d_prim_types); cudaFree(c->d_per_frame); cudaFree(c->d_anim); cudaFree(c->d_tri_pos); cudaFree(c->d_tri_nrm);
     cudaFree(c->d_nodes); cudaFree(c->d_sorted); cudaFree(c->d_lbvh_scratch); cudaFree(c->d_fb); cudaFree(c->d_fb_ids);
+    cudaFree(c->d_wide); cudaFree(c->d_top); cudaFree(c->d_n_top);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     for (int i = 0; i < kStagingSlots; i++) {
         if (c->h_staging[i]) cudaFreeHost(c->h_staging[i]);
@@ -564,10 +577,14 @@ int gprt_build_accel(gprt_ctx* c) {
     GPRT_CUDA(c, cudaEventRecord(c->ev_build0, c->stream));
     int32_t root = INT32_MIN;
     lbvh_build(c->d_aabbs, c->scene.n_prims, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, &root, c->stream, c->d_prim_types);
+    lbvh_collapse(c->d_nodes, c->scene.n_prims, c->d_wide, c->d_top, c->top_capacity, c->d_n_top, c->stream);
     GPRT_CUDA(c, cudaEventRecord(c->ev_build1, c->stream));
     GPRT_CUDA(c, cudaGetLastError());
+    uint32_t n_top = 0;
+    if (c->scene.n_prims >= 2) GPRT_CUDA(c, cudaMemcpyAsync(&n_top, c->d_n_top, sizeof n_top, cudaMemcpyDeviceToHost, c->stream));
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream)); // blocking, like wait_for_gpu at src/Renderer.cpp:827
     c->scene.root_ref = root;
+    c->scene.n_top = n_top;
     c->have_build_timing = true;
     c->built = true;
     return GPRT_OK;
@@ -581,6 +598,7 @@ int gprt_refit_accel(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs) {
     c->h_aabbs.assign(aabbs, aabbs + n_aabbs);
     GPRT_CUDA(c, cudaMemcpyAsync(c->d_aabbs, c->h_aabbs.data(), (size_t)n_aabbs * sizeof(gprt_aabb), cudaMemcpyHostToDevice, c->stream));
     lbvh_refit(c->d_aabbs, n_aabbs, c->d_lbvh_scratch, c->d_nodes, c->d_sorted, c->stream, c->d_prim_types);
+    lbvh_collapse(c->d_nodes, n_aabbs, c->d_wide, c->d_top, c->top_capacity, c->d_n_top, c->stream); // same topology: n_top is unchanged
     GPRT_CUDA(c, cudaGetLastError());
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
     return GPRT_OK;

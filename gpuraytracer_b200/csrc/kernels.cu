@@ -48,7 +48,7 @@ constexpr int kMaxPending = 6;         // candidates kept in registers per ray; 
 constexpr uint32_t kLeafTypeShift = 27; // leaf ref = ~(primitive | type id << 27)
 constexpr uint32_t kLeafPrimMask = (1u << kLeafTypeShift) - 1u;
 
-__device__ __forceinline__ void emit_candidate_now(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t ray, uint32_t prim,
+__device__ __noinline__ void emit_candidate_now(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t ray, uint32_t prim,
                                                    uint32_t type) {
     // warp-aggregated append from divergent code: one atomic per (warp, type)
     const unsigned peers = __match_any_sync(__activemask(), type);
@@ -90,94 +90,15 @@ __device__ __forceinline__ void add_leaf(const SceneDev& sc, const PassParams& p
     add_candidate(pp, wb, ctrl, r, flat, type, pend);
 }
 
-// Walks the subtree under `root` for ray r; every box whose slab test passes on [TMin, tcur] is a candidate.
-// A grazing ray crosses hundreds of boxes (2000+ dependent node fetches at 1 M primitives), and left to one thread
-// that chain, not the throughput, sets the kernel's duration.  So a walk has a node budget (pp.spill_budget), after
-// which the unwalked rest goes to the next spill round as (ray, subtree) entries:
-//   kWalkDepthFirst       no budget (small scenes, last round)
-//   kWalkDepthFirstBudget the main kernel: cheap for the common short ray; the handed-over stack is lopsided (its
-//                         bottom entries are the big far subtrees)
-//   kWalkBreadthFirst     the spill rounds: expanding the oldest entry first opens the top levels of a big subtree,
-//                         so what is handed on are ~budget pieces of similar size and the chain shrinks by that
-//                         factor per round instead of halving
-// The candidate set does not depend on the visiting order.  Returns the nodes fetched.
-enum WalkMode { kWalkDepthFirst = 0, kWalkDepthFirstBudget = 1, kWalkBreadthFirst = 2 };
-constexpr uint32_t kBreadthBudgetMax = 48; // the frontier grows by at most one entry per fetch and must fit the 64-entry ring
-
-template <int MODE, bool MULTI>
-__device__ __forceinline__ uint32_t walk_tree(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, V3 oo, V3 inv_d,
-                                              float tcur, int32_t root, uint32_t inst, uint2* spill_q, uint32_t* spill_count, Pending& pend) {
+// The triangle instances of the TLAS, in TLAS order (the reference has one: the ground quad): Moller-Trumbore, back faces
+// culled, open interval; a shadow ray stops at its first hit.  Updates tcur / key.
+template <bool MULTI>
+__device__ __forceinline__ void plane_triangles(const SceneDev& sc, V3 o, V3 d, bool shadow, float& tcur, unsigned long long& key) {
     const float tmin = 0.0f;
-    const uint32_t flat0 = MULTI ? inst * sc.n_prims : 0u; // candidates are numbered instance * n_prims + primitive
-    int32_t ring[64];
-    uint32_t head = 0, tail = 0; // live entries: ring[head .. tail) mod 64
-    ring[tail++] = root;
-    uint32_t visits = 0;
-    uint32_t budget = 0xFFFFFFFFu;
-    if (MODE == kWalkDepthFirstBudget && pp.spill_budget) budget = pp.spill_budget;
-    if (MODE == kWalkBreadthFirst) budget = min(max(pp.spill_budget, 1u), kBreadthBudgetMax);
-    while (tail != head) {
-        if (MODE != kWalkDepthFirst && visits >= budget) {
-            const uint32_t n = tail - head;
-            const uint32_t at = atomicAdd(spill_count, n);
-            if (at + n <= wb.spill_capacity) {
-                for (uint32_t i = 0; i < n; i++) spill_q[at + i] = make_uint2(MULTI ? (r | (inst << kSpillRayBits)) : r, (uint32_t)ring[(head + i) & 63u]);
-                break;
-            }
-            // queue full: void the reserved slots that exist and finish the walk here
-            for (uint32_t i = 0; i < n && at + i < wb.spill_capacity; i++) spill_q[at + i] = make_uint2(0xFFFFFFFFu, 0u);
-            budget = 0xFFFFFFFFu;
-        }
-        const bool oldest_first = MODE == kWalkBreadthFirst && budget != 0xFFFFFFFFu;
-        const int32_t node = oldest_first ? ring[head++ & 63u] : ring[--tail & 63u];
-        visits++;
-        const float4* n4 = sc.bvh_nodes + 4 * (size_t)node;
-        const float4 a = __ldg(n4), b = __ldg(n4 + 1), c = __ldg(n4 + 2), e = __ldg(n4 + 3);
-        const float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {a.w, b.x, b.y};
-        const float lo1[3] = {b.z, b.w, c.x}, hi1[3] = {c.y, c.z, c.w};
-        const int32_t ref0 = __float_as_int(e.x), ref1 = __float_as_int(e.y);
-        if (slab_test(oo, inv_d, lo0, hi0, tmin, tcur)) {
-            if (ref0 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref0, pend);
-            else if (tail - head < 64u) ring[tail++ & 63u] = ref0;
-            else ctrl->overflow = 1u; // never drop a subtree silently: the dispatch reports GPRT_E_QUEUE_OVERFLOW
-        }
-        if (slab_test(oo, inv_d, lo1, hi1, tmin, tcur)) {
-            if (ref1 < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, r, flat0, (uint32_t)~ref1, pend);
-            else if (tail - head < 64u) ring[tail++ & 63u] = ref1;
-            else ctrl->overflow = 1u;
-        }
-    }
-    return visits;
-}
-
-// One ray: plane, then the AABB tree.  Writes hitkey / ray_tcur, collects candidates in `pend`.
-template <bool PRIMARY, bool MULTI>
-__device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, uint32_t r,
-                                                 Pending& pend) {
-    V3 o, d;
-    uint32_t meta;
-    if (PRIMARY) {
-        const uint32_t px = pp.tile_x + r % pp.tile_w, py = pass_global_row(pp, r / pp.tile_w);
-        generate_camera_ray(px, py, pp.fc, o, d);
-        meta = make_meta(r, 1u, 0u);
-        wb.ray_o[pq][r] = make_float4(o.x, o.y, o.z, 0.0f);
-        wb.ray_d[pq][r] = make_float4(d.x, d.y, d.z, __uint_as_float(meta));
-    } else {
-        const float4 ro = wb.ray_o[pq][r], rd = wb.ray_d[pq][r];
-        o = ld3(ro); d = ld3(rd);
-        meta = __float_as_uint(rd.w);
-    }
-    const bool shadow = meta_shadow(meta) != 0u;
-    const float tmin = 0.0f;
-    float tcur = kRayTMax;
-    unsigned long long key = kKeyMiss;
-
-    // (i) triangle instances, TLAS order (the reference has one: the ground quad)
     const uint32_t n_ti = MULTI ? sc.n_tri_insts : min(sc.n_tri_insts, 1u);
     for (uint32_t ti = 0; ti < n_ti; ti++) {
         const float* w2o = (MULTI && ti) ? sc.tri_insts[ti].w2o : sc.tri_w2o;
         const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
-        bool stop = false;
         for (uint32_t tri = 0; tri < sc.n_tris; tri++) {
             const float* p = sc.tri_pos + 9 * tri;
             const V3 v0 = v3(p[0], p[1], p[2]);
@@ -196,33 +117,51 @@ __device__ __forceinline__ uint32_t traverse_ray(const SceneDev& sc, const PassP
             if (t > tmin && t < tcur) {
                 tcur = t;
                 key = pack_key(t, kCodePlane | ((MULTI ? ti * sc.n_tris : 0u) + tri));
-                if (shadow) { stop = true; break; }
+                if (shadow) return;
             }
         }
-        if (stop) break;
     }
+}
+
+// One ray without the tree: plane, then EVERY AABB of every instance (GPRT_FLAG_BRUTE_FORCE_TRAVERSAL, and scenes of a
+// single primitive, which have no tree).  Writes hitkey / ray_tcur, collects candidates in `pend`.  The LBVH walk is in
+// walk.cuh.
+template <bool PRIMARY, bool MULTI>
+__device__ __forceinline__ void traverse_ray(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, uint32_t r,
+                                             Pending& pend) {
+    V3 o, d;
+    uint32_t meta;
+    if (PRIMARY) {
+        const uint32_t px = pp.tile_x + r % pp.tile_w, py = pass_global_row(pp, r / pp.tile_w);
+        generate_camera_ray(px, py, pp.fc, o, d);
+        meta = make_meta(r, 1u, 0u);
+        wb.ray_o[pq][r] = make_float4(o.x, o.y, o.z, 0.0f);
+        wb.ray_d[pq][r] = make_float4(d.x, d.y, d.z, __uint_as_float(meta));
+    } else {
+        const float4 ro = wb.ray_o[pq][r], rd = wb.ray_d[pq][r];
+        o = ld3(ro); d = ld3(rd);
+        meta = __float_as_uint(rd.w);
+    }
+    const bool shadow = meta_shadow(meta) != 0u;
+    const float tmin = 0.0f;
+    float tcur = kRayTMax;
+    unsigned long long key = kKeyMiss;
+    plane_triangles<MULTI>(sc, o, d, shadow, tcur, key);
     wb.hitkey[r] = key;
     wb.ray_tcur[r] = tcur;
-    if (shadow && key != kKeyMiss) return 0u; // ACCEPT_FIRST_HIT_AND_END_SEARCH
-    if (!sc.has_aabb_instance || sc.n_prims == 0) return 0u;
-
-    // (ii) procedural AABBs, one walk of the (shared) BLAS per TLAS instance in that instance's object space
-    uint32_t visits = 0;
+    if (shadow && key != kKeyMiss) return; // ACCEPT_FIRST_HIT_AND_END_SEARCH
+    if (!sc.has_aabb_instance || sc.n_prims == 0) return;
     const uint32_t n_ai = MULTI ? sc.n_aabb_insts : 1u;
     for (uint32_t k = 0; k < n_ai; k++) {
         const float* w2o = (MULTI && k) ? sc.aabb_insts[k].w2o : sc.aabb_w2o;
         const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
         const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
-        if (pp.brute_force || sc.root_ref < 0) {
-            for (uint32_t i = 0; i < sc.n_prims; i++) {
-                const float* b = sc.aabbs + 6 * i;
-                if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) add_candidate(pp, wb, ctrl, r, (MULTI ? k * sc.n_prims : 0u) + i, sc.prims[(MULTI ? k * sc.n_prims : 0u) + i].type_id, pend);
-            }
-        } else {
-            visits += walk_tree<kWalkDepthFirstBudget, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, sc.root_ref, k, wb.spill[0], &ctrl->spill_count[0], pend);
+        for (uint32_t i = 0; i < sc.n_prims; i++) {
+            const float* b = sc.aabbs + 6 * i;
+            const uint32_t flat = (MULTI ? k * sc.n_prims : 0u) + i;
+            if (slab_test(oo, inv_d, b, b + 3, tmin, tcur)) add_candidate(pp, wb, ctrl, r, flat, sc.prims[flat].type_id, pend);
         }
     }
-    return visits;
 }
 
 // Convergent append of a warp's pending candidates (all 32 lanes call this).
@@ -265,83 +204,21 @@ struct VisitStats {
 };
 
 template <bool PRIMARY, bool MULTI>
-__global__ void __launch_bounds__(kBlock, 6) k_traverse(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                        const __grid_constant__ WaveBuffers wb, int wave) {
+__global__ void __launch_bounds__(kBlock, 6) k_traverse_brute(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+                                                              const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
-    const int lane = threadIdx.x & 31;
     const uint32_t n_rays = PRIMARY ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
-    VisitStats stats;
-    auto walk_batch = [&](uint32_t base) {
-        const uint32_t r = base + (uint32_t)lane;
+    const uint32_t n_round = (n_rays + 31u) & ~31u;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_round; r += gridDim.x * blockDim.x) {
         Pending pend;
         pend.n = 0;
 #pragma unroll
         for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
-        uint32_t visits = 0;
-        if (r < n_rays) visits = traverse_ray<PRIMARY, MULTI>(sc, pp, wb, ctrl, pq, r, pend);
+        if (r < n_rays) traverse_ray<PRIMARY, MULTI>(sc, pp, wb, ctrl, pq, r, pend);
         flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
-        stats.add(visits);
-    };
-    // Ray costs differ a lot, so the last quarter of the rays is handed out in batches of 32 from a shared cursor and
-    // evens out what the fixed stride over the first three quarters left uneven.  (All rays from the cursor costs
-    // one same-address atomic per 32 rays: 0.07 ms at 1080p, a third of this kernel there.)  The next batch is
-    // reserved before the current one is walked, so the atomic's latency hides behind the walk.
-    const uint32_t n_fixed = (n_rays - n_rays / 4u) & ~31u;
-    const uint32_t warps = gridDim.x * (kBlock / 32);
-    for (uint32_t base = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * 32u; base < n_fixed; base += warps * 32u) walk_batch(base);
-    uint32_t base = 0;
-    if (lane == 0) base = n_fixed + atomicAdd(&ctrl->trav_cursor, 32u);
-    base = __shfl_sync(kFull, base, 0);
-    while (base < n_rays) {
-        uint32_t next = 0;
-        if (lane == 0) next = n_fixed + atomicAdd(&ctrl->trav_cursor, 32u);
-        walk_batch(base);
-        base = __shfl_sync(kFull, next, 0);
     }
-    stats.commit(ctrl);
-}
-
-// Spill round `round` (1..kSpillRounds): walks the (ray, subtree) entries the previous round handed over, one per
-// thread, breadth first under the node budget, except the last round, which finishes whatever is left.  Entries are short by construction, so a fixed
-// stride is enough here.
-template <bool MULTI>
-__global__ void __launch_bounds__(kBlock, 6) k_traverse_spill(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
-                                                              const __grid_constant__ WaveBuffers wb, int wave, int round) {
-    __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
-    WaveCtrl* ctrl = &wb.ctrl[wave];
-    const int pq = wave & 1;
-    const uint2* in = wb.spill[(round - 1) & 1];
-    uint2* out = wb.spill[round & 1];
-    const uint32_t n_in = min(ctrl->spill_count[round - 1], wb.spill_capacity);
-    const uint32_t n_round = (n_in + 31u) & ~31u;
-    const bool last = round >= kSpillRounds;
-    VisitStats stats;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
-        Pending pend;
-        pend.n = 0;
-#pragma unroll
-        for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
-        uint32_t visits = 0, r = 0;
-        if (i < n_in) {
-            const uint2 e = in[i];
-            if (e.x != 0xFFFFFFFFu) {
-                r = MULTI ? (e.x & ((1u << kSpillRayBits) - 1u)) : e.x;
-                const uint32_t inst = MULTI ? (e.x >> kSpillRayBits) : 0u;
-                const float* w2o = (MULTI && inst) ? sc.aabb_insts[inst].w2o : sc.aabb_w2o;
-                const V3 o = ld3(wb.ray_o[pq][r]), d = ld3(wb.ray_d[pq][r]);
-                const V3 oo = xform_point_3x4(w2o, o), dd = xform_vector_3x4(w2o, d);
-                const V3 inv_d = v3(1.0f / dd.x, 1.0f / dd.y, 1.0f / dd.z);
-                const float tcur = wb.ray_tcur[r];
-                if (last) visits = walk_tree<kWalkDepthFirst, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, inst, nullptr, nullptr, pend);
-                else visits = walk_tree<kWalkBreadthFirst, MULTI>(sc, pp, wb, ctrl, r, oo, inv_d, tcur, (int32_t)e.y, inst, out, &ctrl->spill_count[round], pend);
-            }
-        }
-        flush_pending(pp, wb, ctrl, r, pend, s_cnt, s_base);
-        stats.add(visits);
-    }
-    stats.commit(ctrl);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -574,6 +451,7 @@ __global__ void __launch_bounds__(kBlock, 5) k_final_color(const __grid_constant
 } // namespace
 } // namespace gprt
 
+#include "walk.cuh"  // k_walk*: the LBVH walk (4-wide nodes, top levels and stack in shared memory, per-lane refill)
 #include "march.cuh" // queue plumbing, analytic tests (same anonymous namespace)
 #include "march_coop.cuh" // k_intersect_coop: warp-cooperative sphere tracer (the production path)
 #include "march_lane.cuh" // k_intersect_lane: per-lane sphere tracer (measured alternative, GPRT_ISECT_VARIANT=2)
@@ -608,15 +486,46 @@ int resident_blocks(const void* kernel) {
     return n;
 }
 
+// Dynamic shared memory of a walk block: the staged top array + its threads' stacks.
+size_t walk_smem(const SceneDev& sc, int threads, int depth) { return (size_t)sc.n_top * 8 * sizeof(float4) + (size_t)threads * depth * sizeof(uint32_t); }
+template <class K> int walk_grid(K kernel, int threads, size_t smem) {
+    // one resident wave of blocks (the kernels are persistent); cached per kernel for the last shared-memory size asked
+    thread_local K cached_kernel = nullptr;
+    thread_local size_t cached_smem = 0;
+    thread_local int cached_grid = 0;
+    if (cached_kernel == kernel && cached_smem == smem && cached_grid) return cached_grid;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
+    if (per_sm < 1) per_sm = 1;
+    cached_kernel = kernel; cached_smem = smem; cached_grid = sm_count() * per_sm;
+    return cached_grid;
+}
+
 template <bool MULTI>
 int launch_traverse_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, cudaStream_t s) {
     const uint32_t upper = (wave == 1) ? pp.n_pixels : pp.ray_capacity;
-    static const int per_sm_primary = resident_blocks((const void*)k_traverse<true, MULTI>), per_sm_secondary = resident_blocks((const void*)k_traverse<false, MULTI>);
-    if (wave == 1) k_traverse<true, MULTI><<<grid_for(upper, per_sm_primary), kBlock, 0, s>>>(sc, pp, wb, wave);
-    else k_traverse<false, MULTI><<<grid_for(upper, per_sm_secondary), kBlock, 0, s>>>(sc, pp, wb, wave);
-    if (!pp.spill_budget) return 1;
-    static const int per_sm_spill = resident_blocks((const void*)k_traverse_spill<MULTI>);
-    for (int round = 1; round <= kSpillRounds; round++) k_traverse_spill<MULTI><<<sm_count() * per_sm_spill, kBlock, 0, s>>>(sc, pp, wb, wave, round);
+    if (pp.brute_force || sc.root_ref < 0) { // no tree to walk: every AABB (test flag; scenes of one primitive)
+        static const int per_sm_primary = resident_blocks((const void*)k_traverse_brute<true, MULTI>), per_sm_secondary = resident_blocks((const void*)k_traverse_brute<false, MULTI>);
+        if (wave == 1) k_traverse_brute<true, MULTI><<<grid_for(upper, per_sm_primary), kBlock, 0, s>>>(sc, pp, wb, wave);
+        else k_traverse_brute<false, MULTI><<<grid_for(upper, per_sm_secondary), kBlock, 0, s>>>(sc, pp, wb, wave);
+        return 1;
+    }
+    if (!pp.spill_budget) {
+        // small scenes: no hand-over rounds (three empty launches per wave would cost more than the walk); the deep-stack
+        // kernel walks every ray to its end
+        const size_t smem = walk_smem(sc, kWalkBlockLast, kStackDepthLast);
+        if (wave == 1) { const int g = walk_grid(k_walk_deep<true, MULTI>, kWalkBlockLast, smem); k_walk_deep<true, MULTI><<<g, kWalkBlockLast, smem, s>>>(sc, pp, wb, wave); }
+        else { const int g = walk_grid(k_walk_deep<false, MULTI>, kWalkBlockLast, smem); k_walk_deep<false, MULTI><<<g, kWalkBlockLast, smem, s>>>(sc, pp, wb, wave); }
+        return 1;
+    }
+    const size_t smem = walk_smem(sc, kWalkBlock, kStackDepth);
+    if (wave == 1) { const int g = walk_grid(k_walk<true, MULTI>, kWalkBlock, smem); k_walk<true, MULTI><<<g, kWalkBlock, smem, s>>>(sc, pp, wb, wave); }
+    else { const int g = walk_grid(k_walk<false, MULTI>, kWalkBlock, smem); k_walk<false, MULTI><<<g, kWalkBlock, smem, s>>>(sc, pp, wb, wave); }
+    const int g_round = walk_grid(k_walk_round<MULTI>, kWalkBlock, smem);
+    for (int round = 1; round < kSpillRounds; round++) k_walk_round<MULTI><<<g_round, kWalkBlock, smem, s>>>(sc, pp, wb, wave, round);
+    const size_t smem_last = walk_smem(sc, kWalkBlockLast, kStackDepthLast);
+    k_walk_last<MULTI><<<walk_grid(k_walk_last<MULTI>, kWalkBlockLast, smem_last), kWalkBlockLast, smem_last, s>>>(sc, pp, wb, wave, kSpillRounds);
     return 1 + kSpillRounds;
 }
 int launch_traverse(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, void* stream) {

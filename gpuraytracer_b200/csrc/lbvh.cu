@@ -241,7 +241,93 @@ __global__ void k_refit(const float* __restrict__ aabbs, const uint32_t* __restr
     }
 }
 
+
+// ---- 4-wide collapse ------------------------------------------------------------------------------
+// The walk moves one node per dependent fetch, so a binary tree costs a fetch per level; with two levels per node the
+// same boxes are tested in half the fetches (the tests of a node's four children are independent: ILP instead of a
+// dependency).  Wide node i is built from binary node i: each child that is a leaf keeps its slot, each internal child
+// is replaced by ITS two children.  Every binary node gets a wide node (one thread each, no ordering between them);
+// only those on even levels below the root are ever reached.  128 bytes, SoA so a thread tests four boxes per float4:
+//   [0] lo.x[4]  [1] lo.y[4]  [2] lo.z[4]  [3] hi.x[4]  [4] hi.y[4]  [5] hi.z[4]  [6] refs[4] (int bits)  [7] unused
+// ref >= 0: wide node index; < 0: leaf (~(primitive | tag << 27)); kWideInvalid: empty slot.  The boxes are the binary
+// tree's, bit for bit, so the walk's slab test sees the same numbers.
+__global__ void k_collapse4(const float4* __restrict__ nodes, int n_internal, float4* __restrict__ wide) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_internal) return;
+    float lo[4][3], hi[4][3];
+    int32_t ref[4];
+    int n = 0;
+    auto take = [&](const float4* nd, int which) { // child `which` of binary node nd
+        const float4 a = nd[0], b = nd[1], c = nd[2], e = nd[3];
+        if (which == 0) { lo[n][0] = a.x; lo[n][1] = a.y; lo[n][2] = a.z; hi[n][0] = a.w; hi[n][1] = b.x; hi[n][2] = b.y; ref[n] = __float_as_int(e.x); }
+        else { lo[n][0] = b.z; lo[n][1] = b.w; lo[n][2] = c.x; hi[n][0] = c.y; hi[n][1] = c.z; hi[n][2] = c.w; ref[n] = __float_as_int(e.y); }
+        n++;
+    };
+    const float4* me = nodes + 4 * (size_t)i;
+    const float4 e = me[3];
+    const int32_t r[2] = {__float_as_int(e.x), __float_as_int(e.y)};
+    for (int c = 0; c < 2; c++) {
+        if (r[c] < 0) take(me, c);
+        else { const float4* ch = nodes + 4 * (size_t)r[c]; take(ch, 0); take(ch, 1); }
+    }
+    for (; n < 4; n++) {
+        for (int k = 0; k < 3; k++) { lo[n][k] = __builtin_inff(); hi[n][k] = -__builtin_inff(); }
+        ref[n] = kWideInvalid;
+    }
+    float4* out = wide + 8 * (size_t)i;
+    for (int k = 0; k < 3; k++) {
+        out[k] = make_float4(lo[0][k], lo[1][k], lo[2][k], lo[3][k]);
+        out[3 + k] = make_float4(hi[0][k], hi[1][k], hi[2][k], hi[3][k]);
+    }
+    out[6] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), __int_as_float(ref[2]), __int_as_float(ref[3]));
+    out[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+// ---- the top of the tree, packed for shared memory --------------------------------------------------
+// Breadth first from the root, `capacity` nodes at most: top[j] is a copy of a wide node whose child refs point INTO the
+// array (kWideTopFlag | index) wherever the child made it in, and to the global array otherwise.  The walk kernels copy
+// the array into shared memory once per block; every ray starts there.  One block; the frontier of a level is processed
+// between two barriers.  *n_top = nodes written.
+__global__ void k_build_top(const float4* __restrict__ wide, int32_t root, uint32_t capacity, float4* __restrict__ top, uint32_t* n_top) {
+    extern __shared__ int32_t s_ids[]; // [capacity]: wide node index of top[j]
+    __shared__ uint32_t s_count;
+    if (threadIdx.x == 0) { s_ids[0] = root; s_count = 1u; }
+    __syncthreads();
+    uint32_t begin = 0;
+    for (;;) {
+        const uint32_t end = s_count < capacity ? s_count : capacity;
+        __syncthreads();
+        if (begin >= end) break;
+        for (uint32_t j = begin + threadIdx.x; j < end; j += blockDim.x) {
+            const float4* src = wide + 8 * (size_t)s_ids[j];
+            float4 refs = src[6];
+            int32_t r[4] = {__float_as_int(refs.x), __float_as_int(refs.y), __float_as_int(refs.z), __float_as_int(refs.w)};
+            for (int k = 0; k < 4; k++) {
+                if (r[k] < 0 || r[k] == kWideInvalid) continue;
+                const uint32_t at = atomicAdd(&s_count, 1u);
+                if (at < capacity) { s_ids[at] = r[k]; r[k] = (int32_t)(kWideTopFlag | at); }
+            }
+            float4* dst = top + 8 * (size_t)j;
+            for (int k = 0; k < 6; k++) dst[k] = src[k];
+            dst[6] = make_float4(__int_as_float(r[0]), __int_as_float(r[1]), __int_as_float(r[2]), __int_as_float(r[3]));
+            dst[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+        begin = end;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_top = s_count < capacity ? s_count : capacity;
+}
+
 } // namespace
+
+int lbvh_collapse(const float4* d_nodes, uint32_t n, float4* d_wide, float4* d_top, uint32_t top_capacity, uint32_t* d_n_top, void* stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (n < 2) return 0;
+    const int n_internal = (int)n - 1;
+    k_collapse4<<<(n_internal + kBlock - 1) / kBlock, kBlock, 0, s>>>(d_nodes, n_internal, d_wide);
+    k_build_top<<<1, 256, top_capacity * sizeof(int32_t), s>>>(d_wide, 0, top_capacity, d_top, d_n_top);
+    return 2;
+}
 
 size_t lbvh_scratch_bytes(uint32_t n) {
     const size_t n_warps = (n + kKeysPerWarp - 1) / kKeysPerWarp;

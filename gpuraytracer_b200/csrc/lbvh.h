@@ -20,6 +20,13 @@ int lbvh_build(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_node
 int lbvh_refit(const float* d_aabbs, uint32_t n, void* d_scratch, float4* d_nodes, const uint32_t* d_sorted_prims, void* stream,
                const uint8_t* d_prim_tags = nullptr);
 
+// The 4-wide form the traversal walks (lbvh.cu, "4-wide collapse"): d_wide holds 8 float4 per binary internal node
+// (n - 1 nodes), d_top the first `top_capacity` nodes breadth first with refs into itself (staged in shared memory by the
+// walk kernels), *d_n_top how many of them exist.  Call after lbvh_build / lbvh_refit.  Returns kernels launched.
+constexpr int32_t kWideInvalid = 0x7FFFFFFF;   // empty child slot
+constexpr uint32_t kWideTopFlag = 0x40000000u; // ref names a node of the staged top array
+int lbvh_collapse(const float4* d_nodes, uint32_t n, float4* d_wide, float4* d_top, uint32_t top_capacity, uint32_t* d_n_top, void* stream);
+
 // FP32 FMA issue-rate probe (fp32_probe.cu): best of a few launches, TFLOP/s.  Returns a cudaError_t.
 int fp32_peak_probe(void* stream, double* tflops);
 

@@ -18,6 +18,7 @@
 #pragma once
 #include <stdint.h>
 
+#include "lbvh.h"
 #include "shade.cuh"
 
 namespace gprt {
@@ -50,10 +51,13 @@ struct InstDev {
     float o2w[12]; // ObjectToWorld3x4()
 };
 constexpr uint32_t kMaxInstancesPerKind = 256; // 8 bits of a spill entry carry the AABB instance
-constexpr uint32_t kSpillRayBits = 23;         // ray slots per pass < 2^23 (gprt_api.cu: kDefaultPassPixels = 2^22)
+constexpr uint32_t kSpillRayBits = 23;         // multi-instance scenes: ray slots per pass < 2^23 (gprt_api.cu: kMaxPassPixelsMulti = 2^22)
 
 struct SceneDev {
-    const float4* bvh_nodes; // 4 x float4 per internal node: child0 min|max, child1 min|max, refs
+    const float4* bvh_nodes; // binary LBVH, 4 x float4 per internal node: child0 min|max, child1 min|max, refs (build / refit only)
+    const float4* wide_nodes; // what the walk reads: 8 x float4 per node, four children (lbvh.cu, k_collapse4)
+    const float4* top_nodes;  // the first n_top wide nodes breadth first, refs into itself: staged in shared memory by every walk block
+    uint32_t n_top;
     int32_t root_ref;        // >= 0 internal node, < 0 leaf (~primitive), INT32_MIN: no primitives
     uint32_t n_prims;
     const float* aabbs;      // 6 floats per primitive (BLAS object space)
@@ -93,6 +97,7 @@ struct WaveCtrl { // one per wave, zeroed at the start of a pass
     uint32_t trav_cursor;       // next unclaimed ray of the wave's traversal (warps claim batches)
     uint32_t node_visits, max_node_visits; // LBVH nodes fetched by the wave; by its longest ray
     uint32_t spill_count[kSpillRounds];    // (ray, subtree) entries handed to spill round i + 1
+    uint32_t spill_cursor[kSpillRounds];   // next unclaimed entry of that round
 };
 
 struct PassParams {
