@@ -6,8 +6,8 @@ The product is libgprt.so (C ABI in include/gprt.h); this package is a thin ctyp
 """
 from ._capi import (GPRT_FLAG_BRUTE_FORCE_TRAVERSAL, GPRT_HIT_AABB, GPRT_HIT_MISS, GPRT_HIT_TRIANGLE, GPRT_MATH_FAST, GPRT_MATH_FMA,
                     GPRT_MATH_PARITY, Config, Counters, GprtError, Rect, Timing)
-from .renderer import Renderer, SceneData, default_config, write_ppm
+from .renderer import MultiRenderer, Renderer, SceneData, default_config, write_ppm
 
-__all__ = ["Renderer", "SceneData", "Config", "Counters", "Timing", "Rect", "GprtError", "default_config", "write_ppm",
+__all__ = ["Renderer", "MultiRenderer", "SceneData", "Config", "Counters", "Timing", "Rect", "GprtError", "default_config", "write_ppm",
            "GPRT_MATH_PARITY", "GPRT_MATH_FAST", "GPRT_FLAG_BRUTE_FORCE_TRAVERSAL", "GPRT_HIT_MISS", "GPRT_HIT_TRIANGLE",
            "GPRT_HIT_AABB"]

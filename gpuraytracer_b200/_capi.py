@@ -153,6 +153,18 @@ def lib():
         "gprt_renderer_context": (vp, [vp]),
         "gprt_renderer_primary_mrays_per_s": (f32, [vp]),
         "gprt_write_ppm": (i32, [C.c_char_p, vp, u32, u32]),
+        "gprt_enable_peer_access": (i32, [vp, i32]),
+        "gprt_multi_create": (i32, [C.POINTER(vp), i32, u32, u32, u32, C.POINTER(i32), i32, C.POINTER(Config)]),
+        "gprt_multi_destroy": (None, [vp]),
+        "gprt_multi_on_init": (i32, [vp]),
+        "gprt_multi_on_update": (i32, [vp, f32, f32, f32]),
+        "gprt_multi_on_render_async": (i32, [vp, vp]),
+        "gprt_multi_do_raytracing_async": (i32, [vp, vp]),
+        "gprt_multi_wait_for_gpu": (i32, [vp]),
+        "gprt_multi_set_frame_count": (i32, [vp, i32]),
+        "gprt_multi_get_size": (i32, [vp, C.POINTER(u32), C.POINTER(u32)]),
+        "gprt_multi_stripe_rows": (u32, [vp]),
+        "gprt_multi_context": (vp, [vp, i32]),
         "gprt_scene_create": (i32, [C.POINTER(vp), i32, u32, u32, u32]),
         "gprt_scene_destroy": (None, [vp]),
         "gprt_scene_update": (i32, [vp, f32, f32, f32]),
@@ -176,6 +188,8 @@ EXPORTED_SYMBOLS = [
     "gprt_set_animation", "gprt_update_transforms", "gprt_get_transforms",
     "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_get_size", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
+    "gprt_enable_peer_access", "gprt_multi_create", "gprt_multi_destroy", "gprt_multi_on_init", "gprt_multi_on_update", "gprt_multi_on_render_async",
+    "gprt_multi_do_raytracing_async", "gprt_multi_wait_for_gpu", "gprt_multi_set_frame_count", "gprt_multi_get_size", "gprt_multi_stripe_rows", "gprt_multi_context",
     "gprt_scene_create", "gprt_scene_destroy", "gprt_scene_update", "gprt_scene_get",
 ]
 

@@ -765,15 +765,15 @@ int gprt_dispatch_stripes_host_async(gprt_ctx* c, const gprt_scene_cb* scene, co
     const uint32_t whole = rows / stripe_rows, tail = rows % stripe_rows;
     if (frame_pitch_bytes == row_bytes) {
         const size_t stripe_bytes = (size_t)stripe_rows * row_bytes;
-        if (whole) GPRT_CUDA(c, cudaMemcpy2DAsync(dst0, stripe_bytes * world, c->d_fb, stripe_bytes, stripe_bytes, whole, cudaMemcpyDeviceToHost, c->stream));
+        if (whole) GPRT_CUDA(c, cudaMemcpy2DAsync(dst0, stripe_bytes * world, c->d_fb, stripe_bytes, stripe_bytes, whole, cudaMemcpyDefault, c->stream));
     } else {
         for (uint32_t k = 0; k < whole; k++)
             GPRT_CUDA(c, cudaMemcpy2DAsync(dst0 + (size_t)k * world * stripe_rows * frame_pitch_bytes, frame_pitch_bytes,
-                                           c->d_fb + (size_t)k * stripe_rows * row_bytes, row_bytes, row_bytes, stripe_rows, cudaMemcpyDeviceToHost, c->stream));
+                                           c->d_fb + (size_t)k * stripe_rows * row_bytes, row_bytes, row_bytes, stripe_rows, cudaMemcpyDefault, c->stream));
     }
     if (tail)
         GPRT_CUDA(c, cudaMemcpy2DAsync(dst0 + (size_t)whole * world * stripe_rows * frame_pitch_bytes, frame_pitch_bytes,
-                                       c->d_fb + (size_t)whole * stripe_rows * row_bytes, row_bytes, row_bytes, tail, cudaMemcpyDeviceToHost, c->stream));
+                                       c->d_fb + (size_t)whole * stripe_rows * row_bytes, row_bytes, row_bytes, tail, cudaMemcpyDefault, c->stream));
     return GPRT_OK;
 }
 
@@ -781,6 +781,18 @@ int gprt_dispatch_host(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_
                        uint32_t height, gprt_rect tile, void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids) {
     const int rc = gprt_dispatch_host_async(c, scene, per_frame, n_per_frame, width, height, tile, h_rgba8, pitch_bytes, h_hit_ids);
     return rc != GPRT_OK ? rc : gprt_sync(c);
+}
+
+int gprt_enable_peer_access(gprt_ctx* c, int peer_device) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    if (peer_device == c->device) return GPRT_OK;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, c->device, peer_device) != cudaSuccess || !can) { cudaGetLastError(); return GPRT_E_UNSUPPORTED; }
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { c->last_cuda_error = (int)e; cudaGetLastError(); return GPRT_E_CUDA; }
+    cudaGetLastError();
+    return GPRT_OK;
 }
 
 void* gprt_get_stream(gprt_ctx* c) { return c ? (void*)c->stream : nullptr; }
@@ -924,7 +936,7 @@ int gprt_last_launch_count(gprt_ctx* c) { return c ? c->last_launches : 0; }
 
 void* gprt_alloc_host(size_t bytes) {
     void* p = nullptr;
-    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) // page-locked for every device of the box { cudaGetLastError(); return nullptr; }
     return p;
 }
 void gprt_free_host(void* p) { if (p) cudaFreeHost(p); }

@@ -6,7 +6,11 @@
 // second and million primary rays per second, here over the whole run.
 //
 //   gprt_render [--scene ID] [--width W --height H] [--grid N] [--frames K] [--time T0] [--dt DT]
-//               [--camera-orbit DEG] [--light-orbit DEG] [--device D] [--in-flight F] [--out PREFIX]
+//               [--camera-orbit DEG] [--light-orbit DEG] [--device D | --devices D0,D1,...] [--in-flight F] [--out PREFIX]
+//
+// --devices cuts every frame into interleaved row stripes over the listed CUDA devices (one context each, one process;
+// a device may be listed more than once) and every device copies its rows straight into the one page-locked host frame
+// the PPM is written from (gprt_multi_*, host/multi_renderer.h).
 //
 // Links against libgprt.so only (no CUDA toolkit needed on the include path).  There is no CPU
 // render path: without an sm_100 GPU the program fails with GPRT_E_NO_DEVICE.
@@ -26,11 +30,12 @@ struct Options {
     uint32_t width = 0, height = 0, grid = 0;
     float t0 = 0.0f, dt = 1.0f / 60.0f, camera_orbit = 0.0f, light_orbit = 0.0f;
     std::string out;
+    std::vector<int> devices; // --devices: one frame over several devices
 };
 
 void usage() {
     std::puts("gprt_render [--scene 0..7] [--width W --height H] [--grid N] [--frames K] [--time T0] [--dt DT]\n"
-              "            [--camera-orbit DEG_PER_FRAME] [--light-orbit DEG_PER_FRAME] [--device D] [--in-flight 1..8] [--out PREFIX]\n"
+              "            [--camera-orbit DEG_PER_FRAME] [--light-orbit DEG_PER_FRAME] [--device D | --devices D0,D1,...] [--in-flight 1..8] [--out PREFIX]\n"
               "scenes: 0 reference scene, 1..5 the BASELINE configs, 6 config 3 with the long march budget, 7 instanced TLAS");
 }
 
@@ -53,6 +58,10 @@ bool parse(int argc, char** argv, Options& o) {
         else if (a == "--camera-orbit") { if (!(v = next("--camera-orbit"))) return false; o.camera_orbit = (float)std::atof(v); }
         else if (a == "--light-orbit") { if (!(v = next("--light-orbit"))) return false; o.light_orbit = (float)std::atof(v); }
         else if (a == "--device") { if (!(v = next("--device"))) return false; o.device = std::atoi(v); }
+        else if (a == "--devices") {
+            if (!(v = next("--devices"))) return false;
+            for (const char* p = v; *p;) { o.devices.push_back(std::atoi(p)); while (*p && *p != ',') p++; if (*p == ',') p++; }
+        }
         else if (a == "--in-flight") { if (!(v = next("--in-flight"))) return false; o.in_flight = std::atoi(v); }
         else if (a == "--out") { if (!(v = next("--out"))) return false; o.out = v; }
         else { std::fprintf(stderr, "gprt_render: unknown option %s\n", a.c_str()); return false; }
@@ -71,12 +80,22 @@ int main(int argc, char** argv) {
     Options o;
     if (!parse(argc, argv, o)) { usage(); return 2; }
     gprt_renderer* r = nullptr;
-    int rc = gprt_renderer_create(&r, o.scene, o.width, o.height, o.grid, o.device, nullptr);
-    if (rc != GPRT_OK) return fail("gprt_renderer_create", rc);
-    if ((rc = gprt_renderer_on_init(r)) != GPRT_OK) { gprt_renderer_destroy(r); return fail("on_init", rc); }
-    if ((rc = gprt_renderer_set_frame_count(r, o.in_flight)) != GPRT_OK) { gprt_renderer_destroy(r); return fail("set_frame_count", rc); }
+    gprt_multi* m = nullptr;
+    int rc;
     uint32_t w = 0, h = 0;
-    gprt_renderer_get_size(r, &w, &h);
+    if (!o.devices.empty()) {
+        rc = gprt_multi_create(&m, o.scene, o.width, o.height, o.grid, o.devices.data(), (int)o.devices.size(), nullptr);
+        if (rc != GPRT_OK) return fail("gprt_multi_create", rc);
+        if ((rc = gprt_multi_on_init(m)) != GPRT_OK) { gprt_multi_destroy(m); return fail("on_init", rc); }
+        if ((rc = gprt_multi_set_frame_count(m, o.in_flight)) != GPRT_OK) { gprt_multi_destroy(m); return fail("set_frame_count", rc); }
+        gprt_multi_get_size(m, &w, &h);
+    } else {
+        rc = gprt_renderer_create(&r, o.scene, o.width, o.height, o.grid, o.device, nullptr);
+        if (rc != GPRT_OK) return fail("gprt_renderer_create", rc);
+        if ((rc = gprt_renderer_on_init(r)) != GPRT_OK) { gprt_renderer_destroy(r); return fail("on_init", rc); }
+        if ((rc = gprt_renderer_set_frame_count(r, o.in_flight)) != GPRT_OK) { gprt_renderer_destroy(r); return fail("set_frame_count", rc); }
+        gprt_renderer_get_size(r, &w, &h);
+    }
     const size_t frame_bytes = (size_t)w * h * 4;
     std::vector<void*> host(o.in_flight, nullptr);
     std::vector<int> frame_of(o.in_flight, -1);
@@ -92,19 +111,21 @@ int main(int argc, char** argv) {
 
     const auto t_begin = std::chrono::steady_clock::now();
     for (int f = 0; f < o.frames && rc == GPRT_OK; f++) {
-        const int slot = gprt_renderer_next_frame_slot(r);
+        const int slot = m ? f % o.in_flight : gprt_renderer_next_frame_slot(r);
         // the slot's previous frame is complete once the *_async call below has waited for it; it is written out
         // first so that its host buffer can be reused (the reference's Present happens at the same point)
         if (frame_of[slot] >= 0) {
-            gprt_ctx* c = gprt_renderer_frame_context(r, slot);
-            if (c && (rc = gprt_sync(c)) != GPRT_OK) break;
+            if (m) rc = gprt_multi_wait_for_gpu(m); // every device's rows of that frame have landed
+            else if (gprt_ctx* c = gprt_renderer_frame_context(r, slot)) rc = gprt_sync(c);
+            if (rc != GPRT_OK) break;
             if ((rc = write_frame(slot)) != GPRT_OK) break;
         }
-        rc = gprt_renderer_on_update(r, o.t0 + o.dt * (float)f, o.camera_orbit, o.light_orbit);
-        if (rc == GPRT_OK) rc = gprt_renderer_on_render_async(r, host[slot]);
+        const float t = o.t0 + o.dt * (float)f;
+        rc = m ? gprt_multi_on_update(m, t, o.camera_orbit, o.light_orbit) : gprt_renderer_on_update(r, t, o.camera_orbit, o.light_orbit);
+        if (rc == GPRT_OK) rc = m ? gprt_multi_on_render_async(m, host[slot]) : gprt_renderer_on_render_async(r, host[slot]);
         frame_of[slot] = f;
     }
-    if (rc == GPRT_OK) rc = gprt_renderer_wait_for_gpu(r);
+    if (rc == GPRT_OK) rc = m ? gprt_multi_wait_for_gpu(m) : gprt_renderer_wait_for_gpu(r);
     const double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
     // the frames still in flight, oldest first
     for (int k = 0; k < o.in_flight && rc == GPRT_OK; k++) {
@@ -117,9 +138,10 @@ int main(int argc, char** argv) {
     }
     if (rc != GPRT_OK) std::fprintf(stderr, "gprt_render: frame loop failed: %s (%d)\n", gprt_error_string(rc), rc);
     else
-        std::printf("scene %d  %ux%u  %d frames  %.3f ms/frame  %.1f fps  ~Million Primary Rays/s: %.1f\n", o.scene, w, h, o.frames,
+        std::printf("scene %d  %ux%u  %zu device context(s)  %d frames  %.3f ms/frame  %.1f fps  ~Million Primary Rays/s: %.1f\n", o.scene, w, h, o.devices.empty() ? (size_t)1 : o.devices.size(), o.frames,
                     seconds * 1e3 / o.frames, o.frames / seconds, (double)w * h * o.frames / seconds / 1e6);
     for (void* p : host) gprt_free_host(p);
-    gprt_renderer_destroy(r);
+    if (m) gprt_multi_destroy(m);
+    else gprt_renderer_destroy(r);
     return rc == GPRT_OK ? 0 : 1;
 }

@@ -234,6 +234,77 @@ class Renderer:
         self.on_destroy()
 
 
+class MultiRenderer:
+    """One frame cut into interleaved row stripes over several CUDA devices from one process (gprt_multi_*,
+    host/multi_renderer.h).  `devices` may name a device more than once: the entries are independent contexts."""
+
+    def __init__(self, scene_id=0, width=0, height=0, grid_n=0, devices=(0,), config: Config = None, frames_in_flight=1):
+        self._lib = lib()
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+        check(self._lib.gprt_multi_create(C.byref(self._h), int(scene_id), int(width), int(height), int(grid_n), arr, len(devices),
+                                          C.byref(config) if config is not None else None), "multi_create")
+        self.devices = list(devices)
+        check(self._lib.gprt_multi_on_init(self._h), "multi_on_init")
+        check(self._lib.gprt_multi_set_frame_count(self._h, int(frames_in_flight)), "multi_set_frame_count")
+        w, h = C.c_uint32(0), C.c_uint32(0)
+        check(self._lib.gprt_multi_get_size(self._h, C.byref(w), C.byref(h)), "multi_get_size")
+        self.width, self.height = int(w.value), int(h.value)
+
+    @property
+    def stripe_rows(self):
+        return int(self._lib.gprt_multi_stripe_rows(self._h))
+
+    def on_update(self, animate_geometry_time=0.0, camera_orbit_deg=0.0, light_orbit_deg=0.0):
+        check(self._lib.gprt_multi_on_update(self._h, float(animate_geometry_time), float(camera_orbit_deg), float(light_orbit_deg)), "multi_on_update")
+
+    def on_render_async(self, h_frame_ptr):
+        """Every device's rows to their global rows of the page-locked host frame at h_frame_ptr."""
+        check(self._lib.gprt_multi_on_render_async(self._h, h_frame_ptr), "multi_on_render_async")
+
+    def do_raytracing_async(self, d_frame_ptr):
+        """The same into a device frame on devices[0] (peer copies)."""
+        check(self._lib.gprt_multi_do_raytracing_async(self._h, d_frame_ptr), "multi_do_raytracing_async")
+
+    def wait_for_gpu(self):
+        check(self._lib.gprt_multi_wait_for_gpu(self._h), "multi_wait_for_gpu")
+
+    def stream(self, i):
+        """cudaStream_t (int) of entry i's frame slot 0."""
+        ctx = self._lib.gprt_multi_context(self._h, int(i))
+        return int(self._lib.gprt_get_stream(ctx) or 0) if ctx else 0
+
+    def on_render(self):
+        """Synchronous: returns the frame as a numpy array (rendered into page-locked memory)."""
+        n = self.width * self.height * 4
+        p = self._lib.gprt_alloc_host(n)
+        if not p:
+            raise MemoryError("gprt_alloc_host")
+        try:
+            self.on_render_async(p)
+            self.wait_for_gpu()
+            return np.frombuffer((C.c_char * n).from_address(p), dtype=np.uint8).reshape(self.height, self.width, 4).copy()
+        finally:
+            self._lib.gprt_free_host(p)
+
+    def close(self):
+        if self._h:
+            self._lib.gprt_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def write_ppm(path, rgba8: np.ndarray):
     h, w = rgba8.shape[:2]
     a = np.ascontiguousarray(rgba8)

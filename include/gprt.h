@@ -290,16 +290,20 @@ int gprt_dispatch_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
                              const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
                              uint32_t width, uint32_t height, gprt_rect tile,
                              void* h_rgba8, size_t pitch_bytes, uint32_t* h_hit_ids);
-/* Multi-GPU with HOST output: renders this rank's stripes (gprt_dispatch_stripes) and copies every row to its GLOBAL row
- * of the caller's full-frame host buffer h_frame_rgba8 (row y at h_frame_rgba8 + y * frame_pitch_bytes), asynchronously on
- * the context stream.  With one host frame shared by all ranks -- cudaHostAlloc(portable) in one process, or shared memory
- * registered with cudaHostRegister in each process -- every GPU delivers its rows over its own PCIe link and nothing is
- * gathered through one device.  gprt_sync() completes it. */
+/* Multi-GPU with a shared full-frame output: renders this rank's stripes (gprt_dispatch_stripes) and copies every row to
+ * its GLOBAL row of the caller's frame h_frame_rgba8 (row y at h_frame_rgba8 + y * frame_pitch_bytes), asynchronously on
+ * the context stream.  The frame may be page-locked host memory shared by all ranks -- gprt_alloc_host in one process,
+ * shared memory registered with cudaHostRegister in each process: every GPU then delivers its rows over its own PCIe link
+ * and nothing is gathered through one device -- or device memory of ANY GPU of the box (unified addressing; a peer copy
+ * over NVLink after gprt_enable_peer_access).  gprt_sync() completes it. */
 int gprt_dispatch_stripes_host_async(gprt_ctx* ctx, const gprt_scene_cb* scene,
                                      const gprt_prim_per_frame* per_frame, uint32_t n_per_frame,
                                      uint32_t width, uint32_t height,
                                      uint32_t stripe_rows, uint32_t rank, uint32_t world,
                                      void* h_frame_rgba8, size_t frame_pitch_bytes);
+/* Let this context's device read / write memory of peer_device directly (cudaDeviceEnablePeerAccess; already enabled is
+ * not an error).  GPRT_E_UNSUPPORTED when the two devices cannot reach each other: copies then go through the host. */
+int gprt_enable_peer_access(gprt_ctx* ctx, int peer_device);
 /* The context's CUDA stream (cudaStream_t as void*). */
 void* gprt_get_stream(gprt_ctx* ctx);
 

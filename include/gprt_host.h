@@ -90,6 +90,25 @@ gprt_ctx* gprt_renderer_context(gprt_renderer* r);
  * src/Renderer.cpp:375-399): million PRIMARY rays per second from the last GPU dispatch time. */
 float gprt_renderer_primary_mrays_per_s(gprt_renderer* r);
 
+/* One frame cut over several CUDA devices from ONE process (host/multi_renderer.h): entry k of `devices` renders the row
+ * stripes k, k + N, ... of every frame with its own context (replicated scene) and copies its rows to their global rows of
+ * the caller's frame -- a page-locked host frame (every GPU over its own PCIe link) or a device frame on devices[0] (peer
+ * copies over NVLink).  A device may appear more than once: {0, 0, 0} renders one frame as three concurrent stripe
+ * dispatches on one GPU, overlapping their serial tails. */
+typedef struct gprt_multi gprt_multi;
+int gprt_multi_create(gprt_multi** out, int scene_id, uint32_t width, uint32_t height, uint32_t grid_n,
+                      const int* devices, int n_devices, const gprt_config* config_override);
+void gprt_multi_destroy(gprt_multi* m);
+int gprt_multi_on_init(gprt_multi* m);
+int gprt_multi_on_update(gprt_multi* m, float animate_geometry_time, float camera_orbit_deg, float light_orbit_deg);
+int gprt_multi_on_render_async(gprt_multi* m, void* h_frame_rgba8);     /* tightly pitched width * height * 4, page-locked */
+int gprt_multi_do_raytracing_async(gprt_multi* m, void* d_frame_rgba8); /* device memory of devices[0]                      */
+int gprt_multi_wait_for_gpu(gprt_multi* m);
+int gprt_multi_set_frame_count(gprt_multi* m, int n);                   /* frames in flight per device (1..8)               */
+int gprt_multi_get_size(gprt_multi* m, uint32_t* width, uint32_t* height);
+uint32_t gprt_multi_stripe_rows(gprt_multi* m);
+gprt_ctx* gprt_multi_context(gprt_multi* m, int i);                     /* frame slot 0 of entry i                          */
+
 /* The CUDA-free scene builder on its own (also exported by libgprt_scene.so, which links no CUDA): the arrays
  * Renderer::initialize_scene / build_geometry / build_shader_tables assemble on the host
  * (src/Renderer.cpp:197-356, 478-565, 732-786, 839-985) for scene_id at animation time t. */

@@ -466,6 +466,56 @@ def test_headless_cli_writes_the_frames_the_library_renders(tmp_path):
             np.testing.assert_array_equal(ppm, img[:, :, :3])
 
 
+def _device_lists():
+    import torch
+    lists = [[0, 0], [0, 0, 0]]                      # several contexts on one GPU: the whole multi-device logic on one device
+    if torch.cuda.device_count() >= 2:
+        lists.append([0, 1])
+    if torch.cuda.device_count() >= 4:
+        lists.append([0, 1, 2, 3])
+    return lists
+
+
+def test_multi_device_renderer_equals_one_dispatch():
+    """gprt_multi_*: one frame cut into interleaved stripes over several device contexts of ONE process, every context
+    copying its rows to their global rows of a shared page-locked host frame / of a device frame on devices[0]: byte for
+    byte the frame of a single gprt_dispatch, for heights that do and do not divide into whole stripes."""
+    import torch
+    from gpuraytracer_b200 import MultiRenderer
+    for (w, h) in ((320, 192), (200, 150)):
+        with Renderer(scene_id=0, width=w, height=h, device=0, config=make_cfg()) as r:
+            r.on_init()
+            r.on_update(0.8)
+            want, _ = r.on_render()
+            want = want.copy()
+        for devices in _device_lists():
+            with MultiRenderer(scene_id=0, width=w, height=h, devices=devices, config=make_cfg()) as m:
+                m.on_update(0.8)
+                np.testing.assert_array_equal(m.on_render(), want)
+                frame = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+                m.do_raytracing_async(frame.data_ptr())
+                m.wait_for_gpu()
+                np.testing.assert_array_equal(frame.cpu().numpy(), want)
+
+
+def test_headless_cli_over_several_devices_writes_the_same_frames(tmp_path):
+    """gprt_render --devices: a C++ caller composes frames over several device contexts without Python; the PPM files are
+    those of the single-device run byte for byte."""
+    import subprocess
+    cli = os.path.join(os.path.dirname(_capi.__file__), "gprt_render")
+    common = ["--scene", "0", "--width", "192", "--height", "108", "--frames", "4", "--time", "0.25", "--dt", "0.5"]
+    one = str(tmp_path / "one")
+    out = subprocess.run([cli, *common, "--out", one], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    for devices in _device_lists():
+        many = str(tmp_path / ("many" + "".join(map(str, devices))))
+        out = subprocess.run([cli, *common, "--devices", ",".join(map(str, devices)), "--out", many], capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+        assert f"{len(devices)} device context(s)" in out.stdout
+        for f in range(4):
+            assert open(f"{many}{f:04d}.ppm", "rb").read() == open(f"{one}{f:04d}.ppm", "rb").read(), (devices, f)
+
+
 def test_empty_and_degenerate_scenes():
     """No procedural primitives at all / a single one (LBVH root is a leaf)."""
     import ctypes as C
