@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(kWalkBlock, 3) k_walk(const __grid_constant__ 
 }
 // small scenes (no hand-over rounds): every ray walked to its end on the deep stack
 template <bool PRIMARY, bool MULTI>
-__global__ void __launch_bounds__(kWalkBlockLast, 4) k_walk_deep(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kWalkBlockLast, 8) k_walk_deep(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                                  const __grid_constant__ WaveBuffers wb, int wave) {
     walk_body<PRIMARY, MULTI, false, kStackDepthLast>(sc, pp, wb, wave, 0, false);
 }
