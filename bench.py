@@ -191,9 +191,6 @@ class Job:
         return v
 
 
-_shm_counter = [0]
-
-
 def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
     """Times `steps` steps of one workload on job.world ranks.  Returns the measurements (every rank; rank 0's are used)."""
     import torch
@@ -228,8 +225,8 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
     full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (mode == "stripes" and rank == 0) else local[j] for j in range(n_slots)]
     # host side of the e2e pass: per slot one [frames_per_step, H, W, 4] block every rank can write (see SharedHostFrames)
     frame_bytes = H * W * 4
-    _shm_counter[0] += 1
-    host = multigpu.SharedHostFrames(f"{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}_{_shm_counter[0]}", n_slots, frames_per_step * frame_bytes,
+    # the same name on every rank of this measurement (ranks may have run different numbers of solo measurements before it)
+    host = multigpu.SharedHostFrames(f"{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}_c{config_id}_{mode}{world}", n_slots, frames_per_step * frame_bytes,
                                      rank, world, barrier=job.barrier)
     flush = [torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev) for _ in range(n_slots)]
 

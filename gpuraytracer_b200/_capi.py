@@ -161,6 +161,7 @@ def lib():
         "gprt_multi_on_render_async": (i32, [vp, vp]),
         "gprt_multi_do_raytracing_async": (i32, [vp, vp]),
         "gprt_multi_wait_for_gpu": (i32, [vp]),
+        "gprt_multi_wait_for_frame_slot": (i32, [vp, i32]),
         "gprt_multi_set_frame_count": (i32, [vp, i32]),
         "gprt_multi_get_size": (i32, [vp, C.POINTER(u32), C.POINTER(u32)]),
         "gprt_multi_stripe_rows": (u32, [vp]),
@@ -189,7 +190,7 @@ EXPORTED_SYMBOLS = [
     "gprt_renderer_wait_for_gpu", "gprt_renderer_frame_context", "gprt_renderer_on_size_changed", "gprt_renderer_scene", "gprt_renderer_get_size", "gprt_renderer_context",
     "gprt_renderer_primary_mrays_per_s", "gprt_write_ppm",
     "gprt_enable_peer_access", "gprt_multi_create", "gprt_multi_destroy", "gprt_multi_on_init", "gprt_multi_on_update", "gprt_multi_on_render_async",
-    "gprt_multi_do_raytracing_async", "gprt_multi_wait_for_gpu", "gprt_multi_set_frame_count", "gprt_multi_get_size", "gprt_multi_stripe_rows", "gprt_multi_context",
+    "gprt_multi_do_raytracing_async", "gprt_multi_wait_for_gpu", "gprt_multi_wait_for_frame_slot", "gprt_multi_set_frame_count", "gprt_multi_get_size", "gprt_multi_stripe_rows", "gprt_multi_context",
     "gprt_scene_create", "gprt_scene_destroy", "gprt_scene_update", "gprt_scene_get",
 ]
 

@@ -87,6 +87,16 @@ int MultiRenderer::wait_for_gpu() {
     return rc;
 }
 
+int MultiRenderer::wait_for_frame_slot(int slot) {
+    int rc = GPRT_OK;
+    for (auto& r : m_r) {
+        gprt_ctx* c = r->frame_context(slot);
+        const int r2 = c ? gprt_sync(c) : GPRT_OK;
+        if (rc == GPRT_OK) rc = r2;
+    }
+    return rc;
+}
+
 } // namespace gprt_host
 
 // ---------------------------------------------------------------------------------------------
@@ -115,6 +125,7 @@ int gprt_multi_on_init(gprt_multi* m) { return m ? m->impl.on_init() : GPRT_E_IN
 int gprt_multi_on_update(gprt_multi* m, float t, float cam_deg, float light_deg) { return m ? m->impl.on_update(t, cam_deg, light_deg) : GPRT_E_INVALID_ARG; }
 int gprt_multi_on_render_async(gprt_multi* m, void* h_frame_rgba8) { return m ? m->impl.on_render_async(h_frame_rgba8) : GPRT_E_INVALID_ARG; }
 int gprt_multi_do_raytracing_async(gprt_multi* m, void* d_frame_rgba8) { return m ? m->impl.do_raytracing_async(d_frame_rgba8) : GPRT_E_INVALID_ARG; }
+int gprt_multi_wait_for_frame_slot(gprt_multi* m, int slot) { return m ? m->impl.wait_for_frame_slot(slot) : GPRT_E_INVALID_ARG; }
 int gprt_multi_wait_for_gpu(gprt_multi* m) { return m ? m->impl.wait_for_gpu() : GPRT_E_INVALID_ARG; }
 int gprt_multi_set_frame_count(gprt_multi* m, int n) { return m ? m->impl.set_frame_count(n) : GPRT_E_INVALID_ARG; }
 int gprt_multi_get_size(gprt_multi* m, uint32_t* width, uint32_t* height) {

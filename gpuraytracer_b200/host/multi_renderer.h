@@ -26,6 +26,7 @@ public:
     int on_render_async(void* h_frame_rgba8);        // host frame, width * 4 bytes per row, page-locked
     int do_raytracing_async(void* d_frame_rgba8);    // device frame on devices[0]
     int wait_for_gpu();
+    int wait_for_frame_slot(int slot);               // the frame last issued on frame slot `slot` has landed from every device
     int set_frame_count(int n);
     void on_destroy();
     uint32_t stripe_rows() const { return m_stripe_rows; }

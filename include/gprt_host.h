@@ -104,6 +104,7 @@ int gprt_multi_on_update(gprt_multi* m, float animate_geometry_time, float camer
 int gprt_multi_on_render_async(gprt_multi* m, void* h_frame_rgba8);     /* tightly pitched width * height * 4, page-locked */
 int gprt_multi_do_raytracing_async(gprt_multi* m, void* d_frame_rgba8); /* device memory of devices[0]                      */
 int gprt_multi_wait_for_gpu(gprt_multi* m);
+int gprt_multi_wait_for_frame_slot(gprt_multi* m, int slot);            /* frame k runs on slot k % frames-in-flight of every device */
 int gprt_multi_set_frame_count(gprt_multi* m, int n);                   /* frames in flight per device (1..8)               */
 int gprt_multi_get_size(gprt_multi* m, uint32_t* width, uint32_t* height);
 uint32_t gprt_multi_stripe_rows(gprt_multi* m);
