@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from gpuraytracer_b200 import GPRT_FLAG_BRUTE_FORCE_TRAVERSAL, GPRT_MATH_FAST, GPRT_MATH_PARITY, GprtError, Renderer, _capi, default_config
+from gpuraytracer_b200 import GPRT_FLAG_BRUTE_FORCE_TRAVERSAL, GPRT_MATH_FAST, GPRT_MATH_FMA, GPRT_MATH_PARITY, GprtError, Renderer, _capi, default_config
 from oracle import oracle
 from tests.golden.make_golden import FIXTURES, HERE as GOLDEN_DIR
 from tests.parity import MAX_MISMATCH, report
@@ -19,7 +19,7 @@ def make_cfg(math_mode=GPRT_MATH_PARITY, flags=0):
     cfg = default_config()
     cfg.math_mode = math_mode
     cfg.flags = flags
-    cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = 0  # keep the scene's own
+    cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = cfg.fractal_iterations = 0  # keep the scene's own
     return cfg
 
 
@@ -86,6 +86,34 @@ def test_fast_math_mode_meets_the_parity_bar(scene_id, w, h, t, grid_n):
     # the pixels beyond 2/255 (shadow-acne pixels flip under any perturbation), so the bound here is 0.2 %.
     rep = check(oracle_render(scene), img, ids, max_mismatch=2e-3, id_slack=max(2, img.shape[0] * img.shape[1] // 100000))
     print(scene_id, rep)
+
+
+@pytest.mark.parametrize("scene_id,w,h,t,grid_n", [(2, 0, 0, 0.25, 0), (3, 960, 540, 0.0, 0), (4, 960, 540, 2.25, 0), (5, 960, 540, 1.0, 64)])
+def test_fma_mode_meets_the_parity_bar(scene_id, w, h, t, grid_n):
+    """GPRT_MATH_FMA: FMA contraction in the sphere tracers only (IEEE div / sqrt, exact transcendentals; the closed-form
+    tests and the fixed-step metaball test stay in the IEEE build because contraction flips whole steps there).  Within the
+    north star's 0.1 % rule on every config (profiles/r02_parity_report_fma.json: worst 0.03 % at BASELINE sizes)."""
+    img, ids, scene, _, _ = gpu_render(scene_id, w, h, t, grid_n, math_mode=GPRT_MATH_FMA)
+    check(oracle_render(scene), img, ids, id_slack=max(2, img.shape[0] * img.shape[1] // 200000))
+
+
+@pytest.mark.parametrize("iters", [2, 6])
+def test_fractal_iterations_knob(iters):
+    """FRACTAL_ITERATIONS_COUNT (src/ConstantBuffers.h:27, used at src/SignedDistanceFractals.hlsli:45) as a run-time field
+    of gprt_config, against the oracle built with the same knob: config 3 (pyramid in every other cell)."""
+    cfg = make_cfg()
+    cfg.fractal_iterations = iters
+    with Renderer(scene_id=3, width=640, height=360, device=0, config=cfg) as r:
+        r.on_init()
+        img, ids = r.on_render(want_hit_ids=True)
+        scene = r.scene()
+    assert scene.config.fractal_iterations == iters
+    orc = oracle.load(metaballs=scene.config.metaballs_count)
+    orc.set_scene(scene)
+    ref = orc.render(scene)
+    check(ref, img, ids)
+    orc.set_scene(scene, fractal_iterations=4)
+    assert (orc.render(scene)["rgba8"] != ref["rgba8"]).mean() > 0.01  # the knob is visible
 
 
 def test_config1_primary_and_shadow_only():
