@@ -7,6 +7,7 @@ import collections
 import csv
 import io
 import json
+import os
 import subprocess
 import sys
 
@@ -42,7 +43,7 @@ def launches(src, dst):
     print(json.dumps(out["kernels"][:8], indent=1))
 
 
-WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread", "launch__grid_size",
+WANT = ["gpu__time_duration.sum", "lts__t_sectors_op_read.sum", "lts__t_sectors_op_write.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread", "launch__grid_size",
         "launch__block_size", "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__issue_active.avg.pct_of_peak_sustained_elapsed",
         "sm__inst_executed.avg.per_cycle_active", "smsp__thread_inst_executed_per_inst_executed.ratio",
         "smsp__thread_inst_executed_per_inst_executed.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -62,7 +63,10 @@ def full(src, dst):
     rows = list(csv.reader(io.StringIO(txt)))
     hdr = rows[0]
     units = dict(zip(hdr, rows[1]))
-    out = {"source": src, "note": "ncu --set full --clock-control none (replayed, cold cache); one entry per captured launch",
+    out = {"source": src, "made_by": " ".join(["python", "tools/ncu_summary.py"] + sys.argv[1:]) + "  (the .ncu-rep is scratch under gpurun_out/ and is not tracked: re-capture it with the "
+                                     "command in the `capture` field on a B200, then re-run this line)",
+           "capture": os.environ.get("NCU_CAPTURE_CMD", ""),
+           "note": "ncu --set full --clock-control none (replayed, cold cache); one entry per captured launch",
            "units": {k: units.get(k, "") for k in WANT if k in units}, "launches": []}
     for r in rows[2:]:
         d = dict(zip(hdr, r))
