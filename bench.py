@@ -131,7 +131,7 @@ def plan_for(config_id, world, args, force_mode=None):
         mode = args.multi_gpu
     else:
         mode = "frames" if W * H <= (1 << 22) else "stripes"
-    n_slots = args.frames_in_flight or (min(8, 2 + world) if mode == "stripes" else 3)
+    n_slots = args.frames_in_flight or (min(8, 2 + world) if mode == "stripes" else 4)
     return {"mode": mode, "n_slots": n_slots, "frames_per_step": world if mode == "frames" else 1,
             "stripe_rows": stripe_rows_for(H, world) if mode == "stripes" else H, "width": W, "height": H}
 
@@ -518,7 +518,7 @@ def roofline(args, conf, device, world, m):
         fp32_peak, peak_src = 74.4, "nominal fallback: 148 SMs x 128 lanes x 2 x 1.965 GHz"
     # DRAM traffic per launch of the same kernel: NOT measured in this run (no profiler here) -- read from the committed ncu --set full
     # capture of the same workload under profiles/ (mean over the launches of one frame); null when none is committed
-    traffic, traffic_src = _committed_traffic(conf, ("r02_ncu_full_k_intersect_coop.json", "r01_ncu_full_k_intersect_coop.json"))
+    traffic, traffic_src = _committed_traffic(conf, "k_intersect_coop", ("r02_ncu_full_frame_config2.json", "r01_ncu_full_k_intersect_coop.json"))
     plan = plan_for(args.config, world, args)
     # FP32 rate of the whole timed pipeline per GPU: the step's frames x flops per frame / the step's time / N GPUs
     pipeline_tflops = flops * plan["frames_per_step"] / (m["ms_per_step"] * 1e-3) / 1e12 / world if m["ms_per_step"] else None
@@ -541,20 +541,20 @@ def roofline(args, conf, device, world, m):
     hbm_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     fin_bytes = W * H * (4 + depth * 4) + int(c.radiance_rays) * 49
     fin_dur = ms[GPRT_K_FINAL] * 1e-3
-    fin_traffic, fin_traffic_src = _committed_traffic(conf, ("r02_ncu_full_k_final_color.json", "r01_ncu_full_k_final_color.json"))
+    fin_traffic, fin_traffic_src = _committed_traffic(conf, "k_final_color", ("r02_ncu_full_frame_config2.json", "r01_ncu_full_k_final_color.json"))
     hbm = {"bound": "hbm", "kernel": "k_final_color", "achieved": round(fin_bytes / fin_dur / 1e9, 1) if fin_dur > 0 else 0.0, "peak": hbm_peak,
            "unit": "GB/s", "frac": round(fin_bytes / fin_dur / 1e9 / hbm_peak, 4) if fin_dur > 0 else 0.0, "traffic": fin_traffic,
            "traffic_source": fin_traffic_src, "peak_source": hbm_src, "bytes_per_launch": fin_bytes}
     return roof, hbm, kernel_ms
 
 
-def _committed_traffic(conf, names):
+def _committed_traffic(conf, kernel, names):
     if conf["scene_id"] != 2:
         return None, None
     for name in names:
         try:
             cap = json.load(open(os.path.join(ROOT, "profiles", name)))
-            vals = [l["dram_bytes_total"] for l in cap["launches"] if "dram_bytes_total" in l]
+            vals = [l["dram_bytes_total"] for l in cap["launches"] if "dram_bytes_total" in l and kernel in l.get("kernel", "")]
             if vals:
                 return round(sum(vals) / len(vals)), f"from the committed capture profiles/{name} (dram__bytes_read.sum + dram__bytes_write.sum, mean per launch), not measured in this run"
         except Exception:
@@ -633,7 +633,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gprt", choices=["gprt", "reference"])
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
-    ap.add_argument("--frames-in-flight", type=int, default=0, help="frame slots (contexts + streams); 0 = 3 on one GPU, min(8, 2 + N) for stripes on N")
+    ap.add_argument("--frames-in-flight", type=int, default=0, help="frame slots (contexts + streams); 0 = 4 for whole frames (measured on one B200: 2 535 / 2 840 / 2 962 / 2 995 Mrays/s at 2 / 3 / 4 / 6), min(8, 2 + N) for stripes on N")
     ap.add_argument("--multi-gpu", default="auto", choices=["auto", "frames", "stripes"],
                     help="N > 1: whole frames round-robin over the ranks, or row stripes of every frame; auto = frames up to 4 Mpixel, stripes above")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development runs of the large configs)")

@@ -91,7 +91,7 @@ def test_bench_plan_and_config_object():
     import bench
     a = _args()
     p1 = bench.plan_for(2, 1, a)
-    assert (p1["mode"], p1["frames_per_step"], p1["n_slots"]) == ("single", 1, 3)
+    assert (p1["mode"], p1["frames_per_step"], p1["n_slots"]) == ("single", 1, 4)
     p8 = bench.plan_for(2, 8, a)
     assert (p8["mode"], p8["frames_per_step"]) == ("frames", 8)
     assert bench.scaling_label(p1) == bench.scaling_label(p8) == "weak"   # one curve, one label
