@@ -15,6 +15,7 @@ GPRT_ABI_VERSION = 2
 GPRT_MATH_PARITY, GPRT_MATH_FAST, GPRT_MATH_FMA = 0, 1, 2
 GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1
 GPRT_FLAG_PROFILE_KERNELS = 2
+GPRT_FLAG_MEGAKERNEL = 4
 GPRT_K_TRAVERSE, GPRT_K_INTERSECT0, GPRT_K_RESOLVE, GPRT_K_SHADE_SPAWN, GPRT_K_FINAL, GPRT_K_INTERSECT_ALL, GPRT_K_COUNT = 0, 1, 11, 12, 13, 14, 15
 GPRT_HIT_MISS = 0xFFFFFFFF
 GPRT_HIT_TRIANGLE = 0x00000000

@@ -39,7 +39,7 @@ UNITS = [
     (os.path.join(HOST, "multi_renderer.cpp"), "multi_renderer.o", []),
 ]
 
-HEADERS = [os.path.join(CSRC, f) for f in ("vecmath.cuh", "prims.cuh", "shade.cuh", "wavefront.cuh", "march.cuh", "march_coop.cuh", "march_lane.cuh", "walk.cuh", "lbvh.h")] + \
+HEADERS = [os.path.join(CSRC, f) for f in ("vecmath.cuh", "prims.cuh", "shade.cuh", "wavefront.cuh", "march.cuh", "march_coop.cuh", "march_lane.cuh", "walk.cuh", "megakernel.cuh", "lbvh.h")] + \
           [os.path.join(HOST, f) for f in ("scene.h", "renderer.h", "multi_renderer.h", "mathx.h")] + \
           [os.path.join(HERE, "..", "include", f) for f in ("gprt.h", "gprt_host.h")]
 

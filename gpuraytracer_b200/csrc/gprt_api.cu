@@ -411,6 +411,10 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     GPRT_CUDA(c, cudaMemsetAsync(c->wb.ctrl, 0, sizeof(WaveCtrl) * (kMaxDepth + 2), c->stream));
     if (D > 1) GPRT_CUDA(c, cudaMemsetAsync(c->wb.lvl_code + pp.n_pixels, 0xFE, sizeof(uint32_t) * (size_t)pp.n_pixels * (D - 1), c->stream));
     int launches = 0;
+    if (c->cfg.flags & GPRT_FLAG_MEGAKERNEL) { // the comparison point: no waves, no queues
+        ScopedInterval si(c, GPRT_K_FINAL);
+        launches += c->kt_isect->megakernel(c->scene, pp, c->wb, ob, (int)c->cfg.metaballs_count, c->stream);
+    } else {
     for (uint32_t wave = 1; wave <= D; wave++) {
         { ScopedInterval si(c, GPRT_K_TRAVERSE); launches += c->kt->traverse(c->scene, pp, c->wb, (int)wave, c->stream); }
         if (c->per_type_launches) {
@@ -435,6 +439,7 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
         { ScopedInterval si(c, GPRT_K_SHADE_SPAWN); launches += c->kt->shade_spawn(c->scene, pp, c->wb, (int)wave, c->stream); }
     }
     { ScopedInterval si(c, GPRT_K_FINAL); launches += c->kt->final_color(c->scene, pp, c->wb, ob, c->stream); }
+    }
     GPRT_CUDA(c, cudaGetLastError());
     if (band < kMaxBands) GPRT_CUDA(c, cudaMemcpyAsync(&c->h_ctrl[band], c->wb.ctrl, sizeof(HostCtrlCopy), cudaMemcpyDeviceToHost, c->stream));
     c->last_launches += launches;
@@ -625,6 +630,7 @@ int dispatch_impl(gprt_ctx* c, const gprt_scene_cb* scene, const gprt_prim_per_f
     }
     c->overflow_reported = false;
 
+    if ((c->cfg.flags & GPRT_FLAG_MEGAKERNEL) && (c->scene.n_prims > 64u || c->scene.n_tri_insts > 1u || c->scene.n_aabb_insts > 1u)) return GPRT_E_UNSUPPORTED;
     // every primitive's instance_index must address the transforms: uploaded now, or already on the device
     // (gprt_update_transforms / an earlier upload) when per_frame is NULL
     if (c->scene.n_prims && (per_frame ? n_per_frame : c->per_frame_valid) <= c->max_instance_index) return GPRT_E_INVALID_ARG;

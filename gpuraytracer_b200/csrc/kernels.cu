@@ -465,6 +465,7 @@ __global__ void __launch_bounds__(kBlock, 5) k_final_color(const __grid_constant
 #include "walk.cuh"  // k_walk*: the LBVH walk (4-wide nodes, top levels and stack in shared memory, per-lane refill)
 #include "march.cuh" // queue plumbing, analytic tests (same anonymous namespace)
 #include "march_coop.cuh" // k_intersect_coop: warp-cooperative sphere tracer (the production path)
+#include "megakernel.cuh" // k_megakernel: one thread per pixel, no queues (the comparison point of SURVEY 7.3, GPRT_FLAG_MEGAKERNEL)
 #include "march_lane.cuh" // k_intersect_lane: per-lane sphere tracer (measured alternative, GPRT_ISECT_VARIANT=2)
 
 namespace gprt {
@@ -646,6 +647,13 @@ int launch_shade_spawn(const SceneDev& sc, const PassParams& pp, const WaveBuffe
     return 1;
 }
 
+int launch_megakernel(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, const OutputBuffers& ob, int metaballs, void* stream) {
+    const int grid = (int)((pp.n_pixels + 127u) / 128u);
+    if (metaballs == 5) k_megakernel<5><<<grid, 128, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
+    else k_megakernel<3><<<grid, 128, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
+    return 1;
+}
+
 int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, const OutputBuffers& ob, void* stream) {
     static const int per_sm = resident_blocks((const void*)k_final_color);
     k_final_color<<<grid_for(pp.n_pixels, per_sm), kBlock, 0, (cudaStream_t)stream>>>(sc, pp, wb, ob);
@@ -656,17 +664,17 @@ int launch_final_color(const SceneDev& sc, const PassParams& pp, const WaveBuffe
 
 #if defined(GPRT_KERNELS_FMA)
 const KernelTable* kernels_fma() {
-    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "fma"};
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, launch_megakernel, "fma"};
     return &t;
 }
 #elif defined(GPRT_KERNELS_FAST)
 const KernelTable* kernels_fast() {
-    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "fast"};
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, launch_megakernel, "fast"};
     return &t;
 }
 #else
 const KernelTable* kernels_parity() {
-    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, "parity"};
+    static const KernelTable t = {launch_traverse, launch_intersect, launch_intersect_all, launch_resolve, launch_shade_spawn, launch_final_color, launch_megakernel, "parity"};
     return &t;
 }
 #endif

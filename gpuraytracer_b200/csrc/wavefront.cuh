@@ -180,6 +180,8 @@ struct KernelTable {
     int (*resolve)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, uint32_t type_mask, void* stream);
     int (*shade_spawn)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, void* stream);
     int (*final_color)(const SceneDev&, const PassParams&, const WaveBuffers&, const OutputBuffers&, void* stream);
+    // the whole frame in one kernel, one thread per pixel (GPRT_FLAG_MEGAKERNEL: the measured comparison point)
+    int (*megakernel)(const SceneDev&, const PassParams&, const WaveBuffers&, const OutputBuffers&, int metaballs, void* stream);
     const char* name;
 };
 

@@ -135,7 +135,10 @@ enum { GPRT_MATH_PARITY = 0, /* IEEE mul/add/div/sqrt, no FMA contraction */
        GPRT_MATH_FAST   = 1, /* FMA contraction + fast intrinsics (what DXIL `fast` allows) */
        GPRT_MATH_FMA    = 2  /* FMA contraction only: IEEE div/sqrt, no flush-to-zero, exact transcendentals (march kernels) */ };
 enum { GPRT_FLAG_BRUTE_FORCE_TRAVERSAL = 1u, /* test every AABB instead of walking the LBVH */
-       GPRT_FLAG_PROFILE_KERNELS = 2u        /* CUDA events around every kernel (gprt_get_kernel_profile) */ };
+       GPRT_FLAG_PROFILE_KERNELS = 2u,       /* CUDA events around every kernel (gprt_get_kernel_profile) */
+       GPRT_FLAG_MEGAKERNEL = 4u             /* the whole frame in ONE kernel, one thread per pixel, no queues: the comparison point
+                                                beside the wavefront form (same image bit for bit; scenes of <= 64 primitives with one
+                                                instance per BLAS, GPRT_E_UNSUPPORTED otherwise) */ };
 
 typedef struct gprt_rect { uint32_t x, y, w, h; } gprt_rect; /* pixel tile, (0,0) = top-left */
 

@@ -116,6 +116,24 @@ def test_fractal_iterations_knob(iters):
     assert (orc.render(scene)["rgba8"] != ref["rgba8"]).mean() > 0.01  # the knob is visible
 
 
+@pytest.mark.parametrize("scene_id,w,h,t", [(0, 480, 270, 0.7), (1, 320, 240, 0.0), (3, 320, 180, 0.0), (4, 320, 180, 2.25)])
+def test_megakernel_comparison_point_renders_the_same_image(scene_id, w, h, t):
+    """GPRT_FLAG_MEGAKERNEL: the whole ray tree of a pixel in one thread, no queues (the comparison point SURVEY 7.3 asks to
+    measure beside the wavefront form).  Same arithmetic, same hit selection: the image, the hit ids and the ray counts are
+    those of the wavefront kernels bit for bit; a scene it does not cover is refused, not rendered wrongly."""
+    from gpuraytracer_b200._capi import GPRT_E_UNSUPPORTED, GPRT_FLAG_MEGAKERNEL
+    a_img, a_ids, scene, a_c, _ = gpu_render(scene_id, w, h, t)
+    b_img, b_ids, _, b_c, launches = gpu_render(scene_id, w, h, t, flags=GPRT_FLAG_MEGAKERNEL)
+    assert launches == 1
+    np.testing.assert_array_equal(a_img, b_img)
+    np.testing.assert_array_equal(a_ids, b_ids)
+    assert (int(a_c.radiance_rays), int(a_c.shadow_rays)) == (int(b_c.radiance_rays), int(b_c.shadow_rays))
+    if scene_id == 0:
+        with pytest.raises(GprtError) as e:
+            gpu_render(5, 96, 54, 1.0, grid_n=16, flags=GPRT_FLAG_MEGAKERNEL)  # 256 primitives
+        assert e.value.status == GPRT_E_UNSUPPORTED
+
+
 def test_config1_primary_and_shadow_only():
     img, ids, scene, c, _ = gpu_render(1, 640, 480)
     ref = oracle_render(scene)
