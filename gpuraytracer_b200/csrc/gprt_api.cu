@@ -56,7 +56,6 @@ struct gprt_ctx {
     PrimRecord* d_prims = nullptr;
     uint32_t spill_capacity_limit = 0; // GPRT_SPILL_CAPACITY (tests: forces the queue-full fallback of the walk)
     uint32_t spill_budget = 0;         // LBVH node fetches per thread before a walk is handed to the next spill round
-    uint32_t priority_queue = 1;       // GPRT_PRIORITY_QUEUE=0 switches the priority end of the candidate queues off (A/B)
     uint32_t pass_pixel_override = 0;  // GPRT_PASS_PIXELS: pixels per internal pass (0 = from the free device memory)
     uint8_t* d_prim_types = nullptr;   // type id per primitive, tagged into the LBVH leaf refs
     float* d_per_frame = nullptr;
@@ -405,7 +404,6 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
     pp.brute_force = (c->cfg.flags & GPRT_FLAG_BRUTE_FORCE_TRAVERSAL) ? 1u : 0u;
     pp.spill_budget = (!pp.brute_force && c->scene.n_prims >= kSpillMinPrims) ? c->spill_budget : 0u;
     pp.stripe_rows = st.rows; pp.stripe_rank = st.rank; pp.stripe_world = st.world;
-    pp.priority_queue = c->priority_queue;
 
     const uint32_t D = pp.max_depth;
     GPRT_CUDA(c, cudaMemsetAsync(c->wb.ctrl, 0, sizeof(WaveCtrl) * (kMaxDepth + 2), c->stream));
@@ -451,8 +449,6 @@ int check_overflow(gprt_ctx* c) {
         for (uint32_t w = 1; w <= c->last_depth; w++) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
             if (wc.overflow) return GPRT_E_QUEUE_OVERFLOW;
-            for (int t = 0; t < kNumTypes; t++) // the two ends of a candidate queue met
-                if ((uint64_t)wc.cand_count[t] + wc.pri_count[t] > c->cand_capacity) return GPRT_E_QUEUE_OVERFLOW;
         }
     return GPRT_OK;
 }
@@ -492,7 +488,6 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     c->kt_isect = (c0.math_mode == GPRT_MATH_FAST) ? kernels_fast() : (c0.math_mode == GPRT_MATH_FMA) ? kernels_fma() : kernels_parity();
     { const char* e = getenv("GPRT_PER_TYPE_LAUNCHES"); c->per_type_launches = e && e[0] == '1'; }
     { const char* e = getenv("GPRT_SPILL_BUDGET"); c->spill_budget = e ? (uint32_t)atoi(e) : kSpillBudget; } // tuning aid
-    { const char* e = getenv("GPRT_PRIORITY_QUEUE"); if (e) c->priority_queue = atoi(e) ? 1u : 0u; }
     { const char* e = getenv("GPRT_TOP_NODES"); if (e && atoi(e) > 0) c->top_capacity = (uint32_t)atoi(e) > 1400u ? 1400u : (uint32_t)atoi(e); }
     { const char* e = getenv("GPRT_PASS_PIXELS"); c->pass_pixel_override = e ? (uint32_t)atoll(e) : 0u; }
     { const char* e = getenv("GPRT_SPILL_CAPACITY"); c->spill_capacity_limit = e ? (uint32_t)atoi(e) : 0u; }
@@ -836,9 +831,9 @@ int gprt_get_counters(gprt_ctx* c, gprt_counters* out) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
             out->radiance_rays += wc.n_radiance;
             out->shadow_rays += wc.n_shadow;
-            out->candidates[0] += (uint64_t)wc.cand_count[0] + wc.cand_count[1] + wc.pri_count[0] + wc.pri_count[1];
-            out->candidates[1] += (uint64_t)wc.cand_count[2] + wc.pri_count[2];
-            for (int t = 3; t < kNumTypes; t++) out->candidates[2] += (uint64_t)wc.cand_count[t] + wc.pri_count[t];
+            out->candidates[0] += (uint64_t)wc.cand_count[0] + wc.cand_count[1];
+            out->candidates[1] += wc.cand_count[2];
+            for (int t = 3; t < kNumTypes; t++) out->candidates[2] += wc.cand_count[t];
             out->queue_overflow += wc.overflow;
         }
     return GPRT_OK;
@@ -869,7 +864,7 @@ int gprt_get_kernel_profile(gprt_ctx* c, gprt_kernel_profile* out) {
     for (int b = 0; b < c->n_bands_last && b < kMaxBands; b++)
         for (uint32_t w = 1; w <= c->last_depth; w++) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
-            for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += (uint64_t)wc.cand_count[t] + wc.pri_count[t]; }
+            for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += wc.cand_count[t]; }
         }
     return GPRT_OK;
 }
@@ -923,7 +918,7 @@ int gprt_get_wave_stats(gprt_ctx* c, uint32_t wave, gprt_wave_stats* out) {
     out->node_visits = wc.node_visits;
     out->max_node_visits = wc.max_node_visits;
     for (int t = 0; t < kNumTypes; t++) {
-        out->candidates[t] = wc.cand_count[t] + wc.pri_count[t];
+        out->candidates[t] = wc.cand_count[t];
         out->work[t] = wc.work[t];
         out->max_evals[t] = wc.max_evals[t];
         for (int b = 0; b < 12; b++) out->evals_hist[t][b] = wc.evals_hist[t][b];

@@ -16,7 +16,6 @@ namespace {
 
 constexpr int kBlock = 256;
 constexpr unsigned kFull = 0xFFFFFFFFu;
-constexpr int kQueueEnds = 32; // per warp: 16 ordinary + 16 priority queue ends (10 types used)
 constexpr int kRefillMin = 8; // idle lanes of a warp that trigger a refill from the queue (measured: 1, 8, 16, 24 within 3 %)
 
 __device__ __forceinline__ unsigned long long pack_key(float t, uint32_t code) {
@@ -49,37 +48,34 @@ constexpr int kMaxPending = 6;         // candidates kept in registers per ray; 
 constexpr uint32_t kLeafTypeShift = 27; // leaf ref = ~(primitive | type id << 27)
 constexpr uint32_t kLeafPrimMask = (1u << kLeafTypeShift) - 1u;
 
-constexpr uint32_t kPendingPri = 0x80000000u; // Pending entry / leaf flag: priority candidate (ray origin inside the box)
-
-__device__ __noinline__ void emit_candidate_now(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t ray, uint32_t prim, uint32_t type,
-                                                bool pri) {
-    // warp-aggregated append from divergent code: one atomic per (warp, queue end)
-    const uint32_t q = type | (pri ? 16u : 0u);
-    const unsigned peers = __match_any_sync(__activemask(), q);
+__device__ __noinline__ void emit_candidate_now(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t ray, uint32_t prim,
+                                                   uint32_t type) {
+    // warp-aggregated append from divergent code: one atomic per (warp, type)
+    const unsigned peers = __match_any_sync(__activemask(), type);
     const int leader = __ffs(peers) - 1;
     const int lane = threadIdx.x & 31;
     uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(pri ? &ctrl->pri_count[type] : &ctrl->cand_count[type], (uint32_t)__popc(peers));
+    if (lane == leader) base = atomicAdd(&ctrl->cand_count[type], (uint32_t)__popc(peers));
     base = __shfl_sync(peers, base, leader);
     const uint32_t idx = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
-    if (idx < pp.cand_capacity) wb.cand[type][pri ? pp.cand_capacity - 1u - idx : idx] = make_uint2(ray, prim);
+    if (idx < pp.cand_capacity) wb.cand[type][idx] = make_uint2(ray, prim);
     else ctrl->overflow = 1u;
 }
 
 struct Pending {
-    uint32_t e[kMaxPending]; // primitive | type << 27 | kPendingPri
+    uint32_t e[kMaxPending]; // primitive | type << 27
     int n;
 };
 
 __device__ __forceinline__ void add_candidate(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t ray, uint32_t prim, uint32_t type,
-                                              Pending& pend, bool pri = false) {
+                                              Pending& pend) {
     if (pend.n < kMaxPending) {
 #pragma unroll
         for (int k = 0; k < kMaxPending; k++)
-            if (k == pend.n) pend.e[k] = prim | (type << kLeafTypeShift) | (pri ? kPendingPri : 0u);
+            if (k == pend.n) pend.e[k] = prim | (type << kLeafTypeShift);
         pend.n++;
     } else {
-        emit_candidate_now(pp, wb, ctrl, ray, prim, type, pri);
+        emit_candidate_now(pp, wb, ctrl, ray, prim, type);
     }
 }
 
@@ -88,10 +84,10 @@ __device__ __forceinline__ void add_candidate(const PassParams& pp, const WaveBu
 // (MULTI = false: the reference's TLAS shape, one instance per BLAS; the kernels are compiled for both.)
 template <bool MULTI>
 __device__ __forceinline__ void add_leaf(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, uint32_t flat0,
-                                         uint32_t tagged, Pending& pend, bool pri = false) {
+                                         uint32_t tagged, Pending& pend) {
     const uint32_t flat = (MULTI ? flat0 : 0u) + (tagged & kLeafPrimMask);
     const uint32_t type = (!MULTI || sc.leaf_types_valid) ? (tagged >> kLeafTypeShift) : sc.prims[flat].type_id;
-    add_candidate(pp, wb, ctrl, r, flat, type, pend, pri);
+    add_candidate(pp, wb, ctrl, r, flat, type, pend);
 }
 
 // The triangle instances of the TLAS, in TLAS order (the reference has one: the ground quad): Moller-Trumbore, back faces
@@ -170,32 +166,27 @@ __device__ __forceinline__ void traverse_ray(const SceneDev& sc, const PassParam
 
 // Convergent append of a warp's pending candidates (all 32 lanes call this).
 __device__ __forceinline__ void flush_pending(const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, uint32_t r, const Pending& pend,
-                                              uint32_t (*s_cnt)[kQueueEnds], uint32_t (*s_base)[kQueueEnds]) {
+                                              uint32_t (*s_cnt)[kNumTypes], uint32_t (*s_base)[kNumTypes]) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (!__any_sync(kFull, pend.n > 0)) return;
-    // queue end q = type (ordinary) or 16 + type (priority); lane q reserves for end q
-    s_cnt[warp][lane] = 0u;
+    if (lane < kNumTypes) s_cnt[warp][lane] = 0u;
     __syncwarp();
     uint32_t rank[kMaxPending];
 #pragma unroll
-    for (int k = 0; k < kMaxPending; k++) {
-        const uint32_t q = ((pend.e[k] >> kLeafTypeShift) & 15u) | ((pend.e[k] & kPendingPri) ? 16u : 0u);
-        rank[k] = (k < pend.n) ? atomicAdd(&s_cnt[warp][q], 1u) : 0u;
-    }
+    for (int k = 0; k < kMaxPending; k++)
+        rank[k] = (k < pend.n) ? atomicAdd(&s_cnt[warp][pend.e[k] >> kLeafTypeShift], 1u) : 0u;
     __syncwarp();
-    {
+    if (lane < kNumTypes) {
         const uint32_t c = s_cnt[warp][lane];
-        const uint32_t type = (uint32_t)lane & 15u;
-        s_base[warp][lane] = (c && type < (uint32_t)kNumTypes) ? atomicAdd(lane >= 16 ? &ctrl->pri_count[type] : &ctrl->cand_count[type], c) : 0u;
+        s_base[warp][lane] = c ? atomicAdd(&ctrl->cand_count[lane], c) : 0u;
     }
     __syncwarp();
 #pragma unroll
     for (int k = 0; k < kMaxPending; k++)
         if (k < pend.n) {
-            const uint32_t type = (pend.e[k] >> kLeafTypeShift) & 15u;
-            const bool pri = (pend.e[k] & kPendingPri) != 0u;
-            const uint32_t idx = s_base[warp][type | (pri ? 16u : 0u)] + rank[k];
-            if (idx < pp.cand_capacity) wb.cand[type][pri ? pp.cand_capacity - 1u - idx : idx] = make_uint2(r, pend.e[k] & kLeafPrimMask);
+            const uint32_t type = pend.e[k] >> kLeafTypeShift;
+            const uint32_t idx = s_base[warp][type] + rank[k];
+            if (idx < pp.cand_capacity) wb.cand[type][idx] = make_uint2(r, pend.e[k] & kLeafPrimMask);
             else ctrl->overflow = 1u;
         }
     __syncwarp();
@@ -215,7 +206,7 @@ struct VisitStats {
 template <bool PRIMARY, bool MULTI>
 __global__ void __launch_bounds__(kBlock, 6) k_traverse_brute(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave) {
-    __shared__ uint32_t s_cnt[kBlock / 32][kQueueEnds], s_base[kBlock / 32][kQueueEnds];
+    __shared__ uint32_t s_cnt[kBlock / 32][kNumTypes], s_base[kBlock / 32][kNumTypes];
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
     const uint32_t n_rays = PRIMARY ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
@@ -261,8 +252,7 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
                                                       const __grid_constant__ WaveBuffers wb, int wave) {
     WaveCtrl* ctrl = &wb.ctrl[wave];
     const int pq = wave & 1;
-    const QueueView qv = queue_view(*ctrl, pp.cand_capacity, TYPE);
-    const uint32_t count = qv.n_total;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
     __shared__ uint32_t s_base;
     uint32_t work = 0;
     for (;;) {
@@ -271,8 +261,8 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
         const uint32_t base = s_base;
         __syncthreads();
         if (base >= count) break;
-        if (base + threadIdx.x >= count) continue;
-        const uint32_t c = queue_slot(qv, base + threadIdx.x);
+        const uint32_t c = base + threadIdx.x;
+        if (c >= count) continue;
         const uint2 cand = wb.cand[TYPE][c];
         const uint32_t r = cand.x, prim = cand.y;
         const float4 rd = wb.ray_d[pq][r];
@@ -321,9 +311,8 @@ __global__ void __launch_bounds__(kBlock) k_resolve(const __grid_constant__ Pass
     const WaveCtrl* ctrl = &wb.ctrl[wave];
     for (int type = 0; type < kNumTypes; type++) {
         if (!((type_mask >> type) & 1u)) continue;
-        const QueueView qv = queue_view(*ctrl, pp.cand_capacity, type);
-        for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < qv.n_total; v += gridDim.x * blockDim.x) {
-            const uint32_t c = queue_slot(qv, v);
+        const uint32_t count = min(ctrl->cand_count[type], pp.cand_capacity);
+        for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < count; c += gridDim.x * blockDim.x) {
             const float4 res = wb.cand_res[type][c];
             if (res.w < 0.0f) continue;
             const uint2 cand = wb.cand[type][c];

@@ -98,15 +98,14 @@ template <int TYPE> __device__ __forceinline__ void publish_miss(const WaveBuffe
 // Analytic types (0 box, 1 spheres): one cheap closed-form test per candidate, no state machine.
 template <int TYPE>
 __device__ __forceinline__ void analytic_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane) {
-    const QueueView qv = queue_view(*ctrl, pp.cand_capacity, TYPE);
-    const uint32_t count = qv.n_total;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
     WarpChunk q;
     uint32_t work = 0;
     for (;;) {
         const uint32_t idx = warp_take(q, true, &ctrl->cursor[TYPE], count, lane);
         if (idx != kNoCand) {
             CandState s;
-            if (fetch_candidate<TYPE>(sc, wb, pq, queue_slot(qv, idx), s)) {
+            if (fetch_candidate<TYPE>(sc, wb, pq, idx, s)) {
                 float thit = 0.0f;
                 V3 n = v3s(0.0f);
                 work++;

@@ -219,8 +219,7 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
                                                int lane, CoopSmem& sm) {
     const int TYPE = SDF + 3;
     constexpr int kTrips = 8; // loop trips between refill checks
-    const QueueView qv = queue_view(*ctrl, pp.cand_capacity, TYPE);
-    const uint32_t count = qv.n_total; // virtual indices: the priority end of the queue first
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
     if (count == 0) return;
     WarpChunk q;
     MarchLane m;
@@ -230,7 +229,7 @@ __device__ __forceinline__ void coop_march_sdf(const int SDF, const SceneDev& sc
     for (;;) {
         poll_committed(wb, TYPE, m);
         const uint32_t idx = warp_take(q, refill_now<RMIN>(m.active) && !m.active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand) fetch_lane(sc, wb, pq, TYPE, queue_slot(qv, idx), m);
+        if (idx != kNoCand) fetch_lane(sc, wb, pq, TYPE, idx, m);
         if (!__any_sync(kFull, m.active)) {
             if (q.exhausted && q.next >= q.end) break;
             continue;
@@ -291,8 +290,7 @@ template <int NB>
 __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, int pq, int lane,
                                                      CoopSmem& sm) {
     constexpr int TYPE = 2;
-    const QueueView qv = queue_view(*ctrl, pp.cand_capacity, TYPE);
-    const uint32_t count = qv.n_total;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
     if (count == 0) return;
     const int warp = threadIdx.x >> 5;
     // warp-private ray list, 12 words per entry, aliased onto the sphere tracer's point list (640 words per warp)
@@ -313,7 +311,7 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
         MarchLane m;
         float tmin = 0.0f, tmax = 0.0f;
         uint32_t mask = 0;
-        if (idx != kNoCand && fetch_lane(sc, wb, pq, TYPE, queue_slot(qv, idx), m)) {
+        if (idx != kNoCand && fetch_lane(sc, wb, pq, TYPE, idx, m)) {
             mask = find_metaball_span<NB>(m.o, m.d, 0.0f, m.tcur, mb, tmin, tmax);
             keep = tmin != __builtin_inff(); // otherwise the field is 0 at every sample
         }

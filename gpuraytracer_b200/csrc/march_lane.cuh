@@ -104,8 +104,7 @@ __device__ __noinline__ void march_sdf_queue(const int SDF, const SceneDev& sc, 
     const int TYPE = SDF + 3;
     constexpr int kTrips = 8; // march steps between refill / export / poll checks
     const int lane = threadIdx.x & 31;
-    const QueueView qv = queue_view(*ctrl, pp.cand_capacity, TYPE);
-    const uint32_t count = qv.n_total;
+    const uint32_t count = min(ctrl->cand_count[TYPE], pp.cand_capacity);
     if (count == 0) return;
     const uint32_t max_steps = pp.sdf_max_steps, iters = pp.fractal_iterations;
     WarpChunk q;
@@ -116,7 +115,7 @@ __device__ __noinline__ void march_sdf_queue(const int SDF, const SceneDev& sc, 
     for (;;) {
         poll_committed(wb, TYPE, m);
         const uint32_t idx = warp_take(q, refill_now<kRefillMin>(m.active) && !m.active, &ctrl->cursor[TYPE], count, lane);
-        if (idx != kNoCand) fetch_lane(sc, wb, pq, TYPE, queue_slot(qv, idx), m);
+        if (idx != kNoCand) fetch_lane(sc, wb, pq, TYPE, idx, m);
         if (!__any_sync(kFull, m.active)) {
             if (q.exhausted && q.next >= q.end) break;
             continue;

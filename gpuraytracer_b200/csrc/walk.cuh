@@ -163,16 +163,7 @@ __device__ __forceinline__ void walk_trips(const SceneDev& sc, const PassParams&
 #pragma unroll
         for (int c = 0; c < 4; c++) {
             if (!((hit >> c) & 1u) || refs[c] == kWideInvalid) continue;
-            if (refs[c] < 0) {
-                // a ray that STARTS inside the box (the secondary rays of a hit on this primitive; every march that uses all its
-                // steps is one of them) is queued at the priority end, so its long dependent chain starts with the launch
-                const float lo[3] = {c == 0 ? lx.x : c == 1 ? lx.y : c == 2 ? lx.z : lx.w, c == 0 ? ly.x : c == 1 ? ly.y : c == 2 ? ly.z : ly.w,
-                                     c == 0 ? lz.x : c == 1 ? lz.y : c == 2 ? lz.z : lz.w};
-                const float hi[3] = {c == 0 ? hx.x : c == 1 ? hx.y : c == 2 ? hx.z : hx.w, c == 0 ? hy.x : c == 1 ? hy.y : c == 2 ? hy.z : hy.w,
-                                     c == 0 ? hz.x : c == 1 ? hz.y : c == 2 ? hz.z : hz.w};
-                const bool inside = w.oo.x >= lo[0] && w.oo.x <= hi[0] && w.oo.y >= lo[1] && w.oo.y <= hi[1] && w.oo.z >= lo[2] && w.oo.z <= hi[2];
-                add_leaf<MULTI>(sc, pp, wb, ctrl, w.r, flat0, (uint32_t)~refs[c], pend, inside && pp.priority_queue);
-            }
+            if (refs[c] < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, w.r, flat0, (uint32_t)~refs[c], pend);
             else if (w.sp < (uint32_t)DEPTH) stack[(size_t)(w.sp++) * blockDim.x] = (uint32_t)refs[c];
             else if (!hand_over<MULTI>(wb, q, q_count, w, stack, 0u, (uint32_t)refs[c], true)) ctrl->overflow = 1u; // full stack: this subtree goes to the
                                                                                                                      // next round; nowhere to put it is an error, never a silent drop
@@ -213,7 +204,7 @@ __device__ __forceinline__ bool begin_ray(const SceneDev& sc, const PassParams& 
 template <bool PRIMARY, bool MULTI, bool ENTRIES, int DEPTH>
 __device__ __forceinline__ void walk_body(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, int round, bool last) {
     extern __shared__ float4 s_dyn[];
-    __shared__ uint32_t s_cnt[kWalkBlock / 32][kQueueEnds], s_base[kWalkBlock / 32][kQueueEnds];
+    __shared__ uint32_t s_cnt[kWalkBlock / 32][kNumTypes], s_base[kWalkBlock / 32][kNumTypes];
     float4* s_top = s_dyn;
     uint32_t* stack = reinterpret_cast<uint32_t*>(s_dyn + 8u * sc.n_top) + threadIdx.x;
     for (uint32_t i = threadIdx.x; i < 8u * sc.n_top; i += blockDim.x) s_top[i] = __ldg(sc.top_nodes + i);

@@ -88,7 +88,6 @@ struct WaveCtrl { // one per wave, zeroed at the start of a pass
     uint32_t n_rays;
     uint32_t n_radiance, n_shadow;
     uint32_t cand_count[kNumTypes];
-    uint32_t pri_count[kNumTypes];  // candidates whose ray STARTS inside the primitive's AABB: queued from the top of the array down, marched first
     uint32_t cursor[kNumTypes];
     uint32_t resolve_cursor;
     uint32_t overflow;
@@ -111,7 +110,6 @@ struct PassParams {
     uint32_t cand_capacity;                  // per type
     uint32_t brute_force;
     uint32_t spill_budget;                   // node fetches per thread before a walk is handed on; 0 = never (small scenes)
-    uint32_t priority_queue;                 // 1: candidates whose ray starts inside the box go to the priority end of their queue
     // multi-GPU row striping: with stripe_world > 1 the pass covers LOCAL rows tile_y .. tile_y+tile_h of
     // rank stripe_rank, local row l being global row ((l / stripe_rows) * stripe_world + stripe_rank) *
     // stripe_rows + l % stripe_rows.  DispatchRaysIndex / Dimensions stay global either way.
@@ -143,23 +141,6 @@ struct WaveBuffers {
     uint32_t* lvl_code;
     uint8_t* lvl_shadow;
 };
-
-// A type's candidate queue is two-ended: ordinary candidates grow from slot 0 up, PRIORITY candidates (the ray's origin is
-// inside the primitive's AABB: the secondary rays of a hit on that primitive, among them every march that uses all 512
-// steps) from slot cap-1 down.  The intersection kernels hand out virtual indices, priority first, so the longest dependent
-// chains of a wave start with the launch instead of wherever the traversal happened to queue them.
-struct QueueView {
-    uint32_t n_pri, n_total, cap;
-};
-__host__ __device__ inline QueueView queue_view(const WaveCtrl& c, uint32_t cap, int type) {
-    QueueView q;
-    q.cap = cap;
-    const uint32_t n = c.cand_count[type] < cap ? c.cand_count[type] : cap;
-    q.n_pri = c.pri_count[type] < cap - n ? c.pri_count[type] : cap - n; // the two ends meeting is a queue overflow (flagged by the writers)
-    q.n_total = n + q.n_pri;
-    return q;
-}
-__host__ __device__ inline uint32_t queue_slot(const QueueView& q, uint32_t v) { return v < q.n_pri ? q.cap - 1u - v : v - q.n_pri; }
 
 struct OutputBuffers {
     uint8_t* rgba8;    // tile row y at rgba8 + y * pitch
