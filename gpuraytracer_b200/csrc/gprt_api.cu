@@ -864,6 +864,8 @@ int gprt_get_kernel_profile(gprt_ctx* c, gprt_kernel_profile* out) {
     for (int b = 0; b < c->n_bands_last && b < kMaxBands; b++)
         for (uint32_t w = 1; w <= c->last_depth; w++) {
             const WaveCtrl& wc = c->h_ctrl[b].ctrl[w];
+            if (dump) std::fprintf(stderr, "gprt wave %u: rays %u + %u, hand-over entries per round %u %u %u, node fetches %u (longest %u)\n", w, wc.n_radiance, wc.n_shadow,
+                                   wc.spill_count[0], wc.spill_count[1], wc.spill_count[2], wc.node_visits, wc.max_node_visits);
             for (int t = 0; t < kNumTypes; t++) { out->work[t] += wc.work[t]; out->candidates[t] += wc.cand_count[t]; }
         }
     return GPRT_OK;

@@ -601,7 +601,11 @@ int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers
 
 // the production path: every primitive type in one persistent launch per wave
 template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
-    static const int grid = persistent_grid(k_intersect_coop<NB, kRefillMin>);
+    static const int grid = [] {
+        const int full = persistent_grid(k_intersect_coop<NB, kRefillMin>);
+        const int lim = isect_blocks_limit(); // GPRT_ISECT_BLOCKS (tuning aid)
+        return (lim > 0 && lim * sm_count() < full) ? lim * sm_count() : full;
+    }();
     k_intersect_coop<NB, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
 template <int NB> void launch_lane_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {

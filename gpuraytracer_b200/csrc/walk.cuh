@@ -18,7 +18,12 @@
 //     wave's cursor, one atomic per chunk, the next chunk requested before the current one runs out; guided chunk sizes so
 //     the warps finish together).
 //   * A node budget per ray (pp.spill_budget fetches): what is left of a long walk is handed to the next of kSpillRounds
-//     rounds as (ray, subtree) entries that other lanes walk in parallel; the last round has no budget and a deep stack.
+//     rounds as (ray, subtree) entries that other lanes walk in parallel.  The two budgeted rounds expand their entries
+//     BREADTH FIRST for kRoundBudget fetches (a 16-entry ring in the same shared-memory column), so a big subtree leaves
+//     them as up to 16 pieces of similar size; the last round walks the pieces to the end depth first on a 48-entry stack.
+//     Lanes of the round kernels are refilled one by one (entries are cheap to start and of every size).  Measured on the
+//     8K frame: the longest walk of any item is 32 fetches (900 without the rounds), the three round launches of a wave
+//     take 0.25 ms instead of 0.6 ms, and a 1/8 stripe of the frame -- one rank of eight -- loses 0.3 ms less per wave.
 //     The candidate set does not depend on the visiting order, so images and hit ids are those of the brute-force loop.
 // Candidates are collected in registers (kMaxPending per ray) and appended to the per-type queues after each batch, where
 // the warp is convergent (flush_pending).
@@ -31,7 +36,8 @@ constexpr int kStackDepth = 16;      // shared-memory stack entries per thread (
 constexpr int kStackDepthLast = 48;  // ... of the last round, which must finish whatever it is handed (128 threads per block)
 constexpr int kWalkBlock = 256;
 constexpr int kWalkBlockLast = 128;
-constexpr uint32_t kChunkMax = 512;  // rays a warp claims from the wave's cursor at once
+constexpr uint32_t kChunkMax = 128;  // rays a warp claims from the wave's cursor at once (512: a 1/8 stripe of an 8K frame is two chunks per warp, too coarse)
+constexpr uint32_t kRoundBudget = 12; // node fetches per entry in the budgeted hand-over rounds (breadth first: see walk_trips)
 constexpr uint32_t kNoItem = 0xFFFFFFFFu;
 
 // The slab test of four child boxes at once: the canonical predicate of slab_test() per child (closed interval, IEEE 1/d,
@@ -103,6 +109,7 @@ struct WalkLane {
     uint32_t r;       // ray slot
     uint32_t inst;    // TLAS instance being walked (MULTI)
     uint32_t sp;      // stack entries
+    uint32_t head;    // FIFO rounds: ring position of the oldest entry (0 in the depth-first kernels)
     uint32_t visits;  // node fetches of this item
     bool busy;
     bool unbounded;   // the hand-over queue was full: this item is walked to its end here
@@ -117,38 +124,42 @@ __device__ __forceinline__ void enter_instance(const SceneDev& sc, WalkLane& w, 
     w.inst = k;
 }
 
-// (ray, subtree) entries handed to the next round: the first `n` stack entries (bottom up) and / or one extra ref.  Returns
-// how many were taken (the queue may be full: slots below its capacity are always written by whoever reserved them, what
-// does not fit stays with the caller).  MULTI packs the instance above the ray slot (kSpillRayBits).
+// (ray, subtree) entries handed to the next round: the `n` stack entries (newest first) and / or one extra ref.  Returns how
+// many were taken (the queue may be full: slots below its capacity are always written by whoever reserved them, what does
+// not fit -- the oldest entries -- stays on the caller's stack).  MULTI packs the instance above the ray slot (kSpillRayBits).
 template <bool MULTI>
 __device__ __noinline__ uint32_t hand_over(const WaveBuffers& wb, uint2* q, uint32_t* q_count, const WalkLane& w, const uint32_t* stack, uint32_t n,
-                                              uint32_t extra_ref, bool has_extra) {
+                                              uint32_t extra_ref, bool has_extra, uint32_t depth) {
     const uint32_t total = n + (has_extra ? 1u : 0u);
     if (!total || !q) return 0u;
     const uint32_t at = atomicAdd(q_count, total);
     const uint32_t fit = at >= wb.spill_capacity ? 0u : min(total, wb.spill_capacity - at);
     const uint32_t tag = MULTI ? (w.r | (w.inst << kSpillRayBits)) : w.r;
-    for (uint32_t i = 0; i < fit; i++) q[at + i] = make_uint2(tag, i < n ? stack[(size_t)i * blockDim.x] : extra_ref);
+    for (uint32_t i = 0; i < fit; i++) q[at + i] = make_uint2(tag, i < n ? stack[(size_t)((w.head + (n - 1u - i)) % depth) * blockDim.x] : extra_ref); // newest first: what does not fit is the oldest, left in place
     return fit;
 }
 
 // This lane's walk of the subtrees on its stack, to the end or to the node budget.  stack: this thread's column of the
 // shared-memory stack.
-template <bool MULTI, int DEPTH>
+// FIFO (the budgeted hand-over rounds): the OLDEST entry is expanded first, so a big subtree is opened breadth first and what
+// is handed on after kRoundBudget fetches are up to DEPTH pieces of similar size -- the longest chain shrinks by that factor
+// per round, where handing over a depth-first stack (whose bottom entries are the big far subtrees) only peels it.
+template <bool MULTI, int DEPTH, bool FIFO = false>
 __device__ __forceinline__ void walk_trips(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, WaveCtrl* ctrl, const float4* s_top, uint32_t* stack,
-                                           WalkLane& w, Pending& pend, uint32_t budget, uint2* q, uint32_t* q_count) {
+                                           WalkLane& w, Pending& pend, uint32_t budget, uint2* q, uint32_t* q_count, int max_trips = 0x7FFFFFFF) {
     const uint32_t flat0 = MULTI ? w.inst * sc.n_prims : 0u;
 #pragma unroll 1
-    while (w.sp != 0u) {
+    for (int trip = 0; trip < max_trips && w.sp != 0u; trip++) {
         if (w.visits >= budget && !w.unbounded) { // the rest of this walk goes to the next round
-            const uint32_t took = hand_over<MULTI>(wb, q, q_count, w, stack, w.sp, 0u, false);
+            const uint32_t took = hand_over<MULTI>(wb, q, q_count, w, stack, w.sp, 0u, false, FIFO ? DEPTH : 0x40000000u);
             if (took == w.sp) { w.sp = 0u; break; }
-            // queue full: keep what did not fit and finish this item here, whatever it takes
-            for (uint32_t i = took; i < w.sp; i++) stack[(size_t)(i - took) * blockDim.x] = stack[(size_t)i * blockDim.x];
+            // queue full: keep what did not fit (the oldest entries) and finish this item here, whatever it takes
             w.sp -= took;
             w.unbounded = true;
         }
-        const uint32_t ref = stack[(size_t)(--w.sp) * blockDim.x];
+        uint32_t ref;
+        if (FIFO) { ref = stack[(size_t)w.head * blockDim.x]; w.head = (w.head + 1u) % DEPTH; w.sp--; }
+        else ref = stack[(size_t)(--w.sp) * blockDim.x]; // depth first: head stays 0
         w.visits++;
         float4 lx, ly, lz, hx, hy, hz, rf;
         if (ref & kWideTopFlag) {
@@ -164,8 +175,8 @@ __device__ __forceinline__ void walk_trips(const SceneDev& sc, const PassParams&
         for (int c = 0; c < 4; c++) {
             if (!((hit >> c) & 1u) || refs[c] == kWideInvalid) continue;
             if (refs[c] < 0) add_leaf<MULTI>(sc, pp, wb, ctrl, w.r, flat0, (uint32_t)~refs[c], pend);
-            else if (w.sp < (uint32_t)DEPTH) stack[(size_t)(w.sp++) * blockDim.x] = (uint32_t)refs[c];
-            else if (!hand_over<MULTI>(wb, q, q_count, w, stack, 0u, (uint32_t)refs[c], true)) ctrl->overflow = 1u; // full stack: this subtree goes to the
+            else if (w.sp < (uint32_t)DEPTH) stack[(size_t)(FIFO ? (w.head + w.sp++) % DEPTH : w.sp++) * blockDim.x] = (uint32_t)refs[c];
+            else if (!hand_over<MULTI>(wb, q, q_count, w, stack, 0u, (uint32_t)refs[c], true, FIFO ? DEPTH : 0x40000000u)) ctrl->overflow = 1u; // full stack: this subtree goes to the
                                                                                                                      // next round; nowhere to put it is an error, never a silent drop
         }
     }
@@ -201,7 +212,7 @@ __device__ __forceinline__ bool begin_ray(const SceneDev& sc, const PassParams& 
 // k_walk: the main traversal kernel of a wave (rays) -- ROUND == 0 -- and its hand-over rounds (entries) -- ROUND > 0.
 // Dynamic shared memory: [n_top * 8 float4 top array][DEPTH * blockDim.x stack words].
 // ---------------------------------------------------------------------------------------------
-template <bool PRIMARY, bool MULTI, bool ENTRIES, int DEPTH>
+template <bool PRIMARY, bool MULTI, bool ENTRIES, int DEPTH, bool FIFO_ROUND = false>
 __device__ __forceinline__ void walk_body(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, int round, bool last) {
     extern __shared__ float4 s_dyn[];
     __shared__ uint32_t s_cnt[kWalkBlock / 32][kNumTypes], s_base[kWalkBlock / 32][kNumTypes];
@@ -233,48 +244,74 @@ __device__ __forceinline__ void walk_body(const SceneDev& sc, const PassParams& 
 
     WarpWork work;
     VisitStats stats;
-    // A batch of 32 consecutive items per warp: neighbouring rays walk nearly the same nodes and take nearly the same
-    // number of fetches (measured lane efficiency 30/32 on primary rays; refilling single lanes as they finish was tried
-    // and lost to the divergent ray set-up it needs: 24/32), and the node budget bounds what the longest ray of a batch
-    // can cost the other 31.
+    if constexpr (ENTRIES) {
+        // Hand-over entries are subtrees of every size (one node to hundreds), and an entry costs nothing to start (its ray
+        // is two loads): here lanes ARE refilled one by one as their entry ends -- kRefillLanes idle lanes trigger a refill,
+        // kEntryTrips fetches run between two checks.  (Measured on the 8K frame, wave 2: batches of 32 entries ran at a
+        // lane efficiency of 0.26 / 0.28 / 0.17 in the three rounds.)
+        constexpr int kRefillLanes = 8, kEntryTrips = 4;
+        WalkLane w;
+        w.busy = false; w.unbounded = false; w.sp = 0; w.head = 0; w.visits = 0; w.r = 0; w.inst = 0; w.tcur = 0.0f;
+        w.oo = v3s(0.0f); w.inv_d = v3s(0.0f);
+        Pending pend;
+        pend.n = 0;
+#pragma unroll
+        for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
+        for (;;) {
+            if (w.busy && w.sp == 0u) { stats.add(w.visits); w.busy = false; }
+            if (__popc(__ballot_sync(kFull, !w.busy)) >= kRefillLanes) {
+                flush_pending(pp, wb, ctrl, w.r, pend, s_cnt, s_base); // convergent; every lane's candidates so far
+                pend.n = 0;
+                const uint32_t idx = take_items(work, !w.busy, cursor, n_items, warps, lane);
+                if (idx != kNoItem) {
+                    const uint2 e = in[idx];
+                    w.r = MULTI ? (e.x & ((1u << kSpillRayBits) - 1u)) : e.x;
+                    const V3 o = ld3(wb.ray_o[pq][w.r]), d = ld3(wb.ray_d[pq][w.r]);
+                    enter_instance<MULTI>(sc, w, o, d, MULTI ? (e.x >> kSpillRayBits) : 0u);
+                    w.tcur = wb.ray_tcur[w.r];
+                    w.visits = 0; w.unbounded = false; w.busy = true;
+                    stack[0] = e.y;
+                    w.sp = 1u; w.head = 0u;
+                }
+                if (!__any_sync(kFull, w.busy)) {
+                    if (!work_left(work)) break;
+                    continue;
+                }
+            }
+            walk_trips<MULTI, DEPTH, FIFO_ROUND>(sc, pp, wb, ctrl, s_top, stack, w, pend, FIFO_ROUND ? min(budget, kRoundBudget) : budget, out, out_count, kEntryTrips);
+        }
+    } else {
+    // A batch of 32 consecutive rays per warp: neighbouring rays walk nearly the same nodes and take nearly the same
+    // number of fetches (measured lane efficiency 31/32 on primary rays; refilling single lanes as they finish was tried
+    // here too and lost to the divergent ray set-up it needs: 24/32), and the node budget bounds what the longest ray of a
+    // batch can cost the other 31.
     for (;;) {
         const uint32_t idx = take_items(work, true, cursor, n_items, warps, lane);
         if (!__any_sync(kFull, idx != kNoItem)) break;
         WalkLane w;
-        w.busy = false; w.unbounded = false; w.sp = 0; w.visits = 0; w.r = 0; w.inst = 0; w.tcur = 0.0f;
+        w.busy = false; w.unbounded = false; w.sp = 0; w.head = 0; w.visits = 0; w.r = 0; w.inst = 0; w.tcur = 0.0f;
         w.oo = v3s(0.0f); w.inv_d = v3s(0.0f);
         Pending pend;
         pend.n = 0;
 #pragma unroll
         for (int k = 0; k < kMaxPending; k++) pend.e[k] = 0u;
         if (idx != kNoItem) {
-            if (!ENTRIES) {
-                V3 o, d;
-                w.r = idx;
-                if (begin_ray<PRIMARY, MULTI>(sc, pp, wb, pq, idx, o, d)) {
-                    w.tcur = wb.ray_tcur[idx];
-                    w.busy = true;
-                    for (uint32_t k = 0; k < n_ai; k++) { // one walk of the shared BLAS per TLAS instance, in that instance's object space
-                        enter_instance<MULTI>(sc, w, o, d, k);
-                        stack[0] = kWideTopFlag; // the root is top[0]
-                        w.sp = 1u;
-                        walk_trips<MULTI, DEPTH>(sc, pp, wb, ctrl, s_top, stack, w, pend, budget, out, out_count);
-                    }
-                }
-            } else {
-                const uint2 e = in[idx];
-                w.r = MULTI ? (e.x & ((1u << kSpillRayBits) - 1u)) : e.x;
-                const V3 o = ld3(wb.ray_o[pq][w.r]), d = ld3(wb.ray_d[pq][w.r]);
-                enter_instance<MULTI>(sc, w, o, d, MULTI ? (e.x >> kSpillRayBits) : 0u);
-                w.tcur = wb.ray_tcur[w.r];
+            V3 o, d;
+            w.r = idx;
+            if (begin_ray<PRIMARY, MULTI>(sc, pp, wb, pq, idx, o, d)) {
+                w.tcur = wb.ray_tcur[idx];
                 w.busy = true;
-                stack[0] = e.y;
-                w.sp = 1u;
-                walk_trips<MULTI, DEPTH>(sc, pp, wb, ctrl, s_top, stack, w, pend, budget, out, out_count);
+                for (uint32_t k = 0; k < n_ai; k++) { // one walk of the shared BLAS per TLAS instance, in that instance's object space
+                    enter_instance<MULTI>(sc, w, o, d, k);
+                    stack[0] = kWideTopFlag; // the root is top[0]
+                    w.sp = 1u; w.head = 0u;
+                    walk_trips<MULTI, DEPTH>(sc, pp, wb, ctrl, s_top, stack, w, pend, budget, out, out_count);
+                }
             }
         }
         flush_pending(pp, wb, ctrl, w.r, pend, s_cnt, s_base); // convergent
         stats.add(w.visits);
+    }
     }
     stats.commit(ctrl);
 }
@@ -286,14 +323,14 @@ __global__ void __launch_bounds__(kWalkBlock, 3) k_walk(const __grid_constant__ 
 }
 // small scenes (no hand-over rounds): every ray walked to its end on the deep stack
 template <bool PRIMARY, bool MULTI>
-__global__ void __launch_bounds__(kWalkBlockLast, 8) k_walk_deep(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kWalkBlockLast, 6) k_walk_deep(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                                  const __grid_constant__ WaveBuffers wb, int wave) {
     walk_body<PRIMARY, MULTI, false, kStackDepthLast>(sc, pp, wb, wave, 0, false);
 }
 template <bool MULTI>
-__global__ void __launch_bounds__(kWalkBlock, 3) k_walk_round(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kWalkBlock, 2) k_walk_round(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, int round) {
-    walk_body<false, MULTI, true, kStackDepth>(sc, pp, wb, wave, round, false);
+    walk_body<false, MULTI, true, kStackDepth, true>(sc, pp, wb, wave, round, false);
 }
 template <bool MULTI>
 __global__ void __launch_bounds__(kWalkBlockLast, 4) k_walk_last(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,

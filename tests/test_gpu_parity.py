@@ -308,8 +308,8 @@ def test_traversal_spill_rounds_do_not_change_the_candidates(monkeypatch, budget
 
 def test_traversal_node_budget_bounds_the_longest_walk():
     """gprt_get_wave_stats: the hand-over rounds bound the longest walk of one entry -- the node budget (32 wide nodes) in the
-    main walk and the budgeted rounds, a few dozen in the last round, which finishes what is left; without the rounds
-    (budget 0) single rays fetch many hundreds."""
+    main walk, 12 in the two breadth-first rounds that cut what is left into pieces of similar size, and what those pieces
+    need in the last round; without the rounds (budget 0) single rays fetch many hundreds."""
     with Renderer(scene_id=5, width=960, height=540, grid_n=256, device=0, config=make_cfg()) as r:
         r.on_init()
         r.on_update(1.0)
@@ -317,7 +317,7 @@ def test_traversal_node_budget_bounds_the_longest_walk():
         for wave in (1, 2, 3):
             s = r.wave_stats(wave)
             assert s.node_visits > 0
-            assert 0 < s.max_node_visits <= 96, (wave, s.max_node_visits)
+            assert 0 < s.max_node_visits <= 48, (wave, s.max_node_visits)
 
 
 def test_config5_million_primitives_tile():
