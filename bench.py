@@ -131,7 +131,9 @@ def plan_for(config_id, world, args, force_mode=None):
         mode = args.multi_gpu
     else:
         mode = "frames" if W * H <= (1 << 22) else "stripes"
-    n_slots = args.frames_in_flight or (min(8, 2 + world) if mode == "stripes" else 4)
+    # whole frames: 4 in flight (measured on one B200, config 2: 2 535 / 2 840 / 2 962 / 2 995 Mrays/s at 2 / 3 / 4 / 6); 3 for
+    # the 8K frame, whose queues are 44 GB per frame context
+    n_slots = args.frames_in_flight or (min(8, 2 + world) if mode == "stripes" else (4 if W * H <= (1 << 22) else 3))
     return {"mode": mode, "n_slots": n_slots, "frames_per_step": world if mode == "frames" else 1,
             "stripe_rows": stripe_rows_for(H, world) if mode == "stripes" else H, "width": W, "height": H}
 
