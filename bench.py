@@ -378,12 +378,14 @@ def strong_scaling(job_all, args, math):
     else:
         dist.barrier()
         plan = plan_for(5, job_all.world, args, force_mode="stripes")
-        mN = measure(job_all, args, 5, plan, steps, warmup, math, latency_steps=3)
+        # N times the frames at N GPUs: every rank then renders as many rays inside the timed window as rank 0 did alone, and the
+        # fill / drain of the frames in flight at the two ends of the window weighs the same in both figures
+        mN = measure(job_all, args, 5, plan, steps * job_all.world, warmup, math, latency_steps=3)
     if job_all.rank != 0:
         return None
     W, H = SIZES[5]
     return {
-        "workload": CONFIGS[5]["workload"], "width": W, "height": H, "n_gpus": job_all.world, "scaling": "strong", "steps": steps, "warmup": warmup,
+        "workload": CONFIGS[5]["workload"], "width": W, "height": H, "n_gpus": job_all.world, "scaling": "strong", "steps": steps * job_all.world, "warmup": warmup,
         "sharding": "one GPU, whole frame" if job_all.world == 1 else f"{plan['stripe_rows']}-row stripes interleaved over {job_all.world} ranks "
                     "(gprt_dispatch_stripes), replicated scene and LBVH, NCCL gather of the RGBA8 rows to rank 0",
         "frames_in_flight": plan["n_slots"], "ms_per_frame": round(mN["frame_ms"], 4), "value": round(mN["value"], 3), "unit": UNIT,
@@ -391,7 +393,8 @@ def strong_scaling(job_all, args, math):
         "rays_per_frame": mN["rays_per_step"],
         "n1": {"ms_per_frame": round(n1["frame_ms"], 4), "value": round(n1["value"], 3), "e2e_value": round(n1["e2e_value"], 3),
                "single_frame_ms": round(n1["single_frame_ms"], 4), "frames_in_flight": plan_for(5, 1, args)["n_slots"],
-               "how": "same run, same steps: rank 0 alone renders whole frames while the other ranks wait"},
+               "steps": steps, "how": "same run, rank 0 alone renders whole frames while the other ranks wait; `steps` frames here, N * `steps` "
+                                      "frames at N GPUs (the same rays per GPU inside either timed window)"},
         "efficiency": round(n1["frame_ms"] / (job_all.world * mN["frame_ms"]), 4),
         "e2e_efficiency": round(mN["e2e_value"] / (job_all.world * n1["e2e_value"]), 4),
         "efficiency_how": "T(1 GPU) / (N * T(N GPUs)) per frame, both with frames in flight, L2 flushed, CUDA events, max over ranks",

@@ -551,9 +551,9 @@ int isect_blocks_limit() {
     return v;
 }
 
-template <class K> int persistent_grid(K kernel) {
+template <class K> int persistent_grid(K kernel, int block = kCoopBlock) {
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0);
     if (per_sm < 1) per_sm = 1;
     return sm_count() * per_sm;
 }
@@ -563,18 +563,18 @@ template <int TYPE, int NB> void launch_intersect_t(const SceneDev& sc, const Pa
     if constexpr (TYPE >= 3) {
         if (!stats_kernels()) {
             static const int grid = persistent_grid(k_coop_sdf<TYPE - 3, kRefillMin>);
-            k_coop_sdf<TYPE - 3, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+            k_coop_sdf<TYPE - 3, kRefillMin><<<grid, kCoopBlock, 0, s>>>(sc, pp, wb, wave);
             return;
         }
     }
     if constexpr (TYPE == 2) {
         if (!stats_kernels()) {
             static const int grid = persistent_grid(k_scan_metaballs<NB>);
-            k_scan_metaballs<NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
+            k_scan_metaballs<NB><<<grid, kCoopBlock, 0, s>>>(sc, pp, wb, wave);
             return;
         }
     }
-    static const int grid = persistent_grid(k_intersect<TYPE, NB>);
+    static const int grid = persistent_grid(k_intersect<TYPE, NB>, kBlock);
     k_intersect<TYPE, NB><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave);
 }
 
@@ -606,17 +606,17 @@ template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, c
         const int lim = isect_blocks_limit(); // GPRT_ISECT_BLOCKS (tuning aid)
         return (lim > 0 && lim * sm_count() < full) ? lim * sm_count() : full;
     }();
-    k_intersect_coop<NB, kRefillMin><<<grid, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
+    k_intersect_coop<NB, kRefillMin><<<grid, kCoopBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
 template <int NB> void launch_lane_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
     static const int per_sm = [] {
         int n = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_intersect_lane<NB>, kBlock, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_intersect_lane<NB>, kCoopBlock, 0);
         if (n < 1) n = 1;
         const int lim = isect_blocks_limit();
         return (lim > 0 && lim < n) ? lim : n;
     }();
-    k_intersect_lane<NB><<<sm_count() * per_sm, kBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
+    k_intersect_lane<NB><<<sm_count() * per_sm, kCoopBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
 int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {
     if (isect_variant() == 2) {

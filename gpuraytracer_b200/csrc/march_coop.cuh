@@ -26,7 +26,11 @@
 namespace gprt {
 namespace {
 
-constexpr int kWarpsPerBlock = kBlock / 32;
+#ifndef GPRT_COOP_BLOCK
+#define GPRT_COOP_BLOCK 256
+#endif
+constexpr int kCoopBlock = GPRT_COOP_BLOCK; // threads per block of the persistent march kernels
+constexpr int kWarpsPerBlock = kCoopBlock / 32;
 constexpr int kCoopPts = 32 * 5; // worst case: every lane posts 5 points
 
 struct CoopSmem { // warp-private scratch
@@ -389,7 +393,7 @@ __device__ __forceinline__ void scan_metaballs_queue(const SceneDev& sc, const P
 // the warps resident on one SM run the same code (measured: with a per-warp rotation
 // stall_no_instruction became the top stall).
 template <int NB, int RMIN>
-__global__ void __launch_bounds__(kBlock, 4) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kCoopBlock, 1024 / kCoopBlock) k_intersect_coop(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
     __shared__ CoopSmem sm;
     WaveCtrl* ctrl = &wb.ctrl[wave];
@@ -410,14 +414,14 @@ __global__ void __launch_bounds__(kBlock, 4) k_intersect_coop(const __grid_const
 
 // one SDF type per launch (profiling mode)
 template <int SDF, int RMIN>
-__global__ void __launch_bounds__(kBlock) k_coop_sdf(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kCoopBlock) k_coop_sdf(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                      const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ CoopSmem sm;
     coop_march_sdf<RMIN>(SDF, sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);
 }
 
 template <int NB>
-__global__ void __launch_bounds__(kBlock) k_scan_metaballs(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kCoopBlock) k_scan_metaballs(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                            const __grid_constant__ WaveBuffers wb, int wave) {
     __shared__ CoopSmem sm;
     scan_metaballs_queue<NB>(sc, pp, wb, &wb.ctrl[wave], wave & 1, threadIdx.x & 31, sm);

@@ -147,7 +147,7 @@ __device__ __noinline__ void march_sdf_queue(const int SDF, const SceneDev& sc, 
 
 // ---- all types in one persistent launch (see k_intersect_coop for the order and the %smid rotation) ----
 template <int NB>
-__global__ void __launch_bounds__(kBlock, 4) k_intersect_lane(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
+__global__ void __launch_bounds__(kCoopBlock, 1024 / kCoopBlock) k_intersect_lane(const __grid_constant__ SceneDev sc, const __grid_constant__ PassParams pp,
                                                               const __grid_constant__ WaveBuffers wb, int wave, uint32_t type_mask) {
     __shared__ CoopSmem sm;
     WaveCtrl* ctrl = &wb.ctrl[wave];
