@@ -16,7 +16,9 @@ N > 1 (one process per GPU, torchrun):
     step is N frames): "scaling": "weak", at every N including 1.
   * the north-star split -- ONE image tile-sharded over the GPUs -- is measured in the same run on the configuration
     the north star names for it (config 5: 7680x4320, 1 M primitives) and reported in the same JSON line as
-    `strong_scaling`: interleaved row stripes of every frame, replicated scene, NCCL gather of the rows to rank 0,
+    `strong_scaling`: interleaved row stripes of every frame, replicated scene, every rank's rows written straight to
+    their place in rank 0's device frame over NVLink (peer memory; the ranks' frame streams meet in a 4-byte NCCL
+    all-reduce; --composite gather: NCCL gather of packed stripes + an un-interleave pass instead),
     with the one-GPU figure it is relative to measured in the same run (rank 0 alone, the other ranks idle).
 `e2e` at N > 1: every rank copies its frames / rows straight into one host frame shared by all ranks (shared memory,
 page-locked in each process), so the pixels leave over N PCIe links and nothing is gathered through rank 0's GPU.
@@ -138,13 +140,18 @@ def plan_for(config_id, world, args, force_mode=None):
             "stripe_rows": stripe_rows_for(H, world) if mode == "stripes" else H, "width": W, "height": H}
 
 
+STRIPE_COMPOSITE = {"peer": "each rank's RGBA8 rows copied straight to their global rows of rank 0's device frame over NVLink (CUDA IPC peer memory, "
+                            "gprt_dispatch_stripes_host_async), one 4-byte NCCL all-reduce per frame as the barrier of the ranks' frame streams",
+                    "gather": "NCCL gather of the packed RGBA8 stripe buffers to rank 0 + an un-interleave pass there"}
+
+
 def config_object(config_id, world, args, plan):
     """The `config` of the JSON line: a function of the command line only, so that the reference arm prints the same object."""
     mode, srows = plan["mode"], plan["stripe_rows"]
     par = {"single": "1 GPU",
            "frames": f"{world} GPUs, whole frames round-robin (frame g on rank g % {world}), replicated scene, NCCL gather of the RGBA8 frames to rank 0; "
                      f"a step is {world} frames, one per rank",
-           "stripes": f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, NCCL gather of the RGBA8 rows to rank 0"}[mode]
+           "stripes": f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, " + STRIPE_COMPOSITE[args.composite]}[mode]
     return {"workload": CONFIGS[config_id]["workload"], "width": plan["width"], "height": plan["height"], "math_mode": args.math,
             "frames_in_flight": plan["n_slots"], "multi_gpu": mode, "frames_per_step": plan["frames_per_step"],
             "l2_flush": f"{L2_FLUSH_BYTES >> 20} MiB memset on the frame's stream before every timed step, device-output and host-output passes alike "
@@ -221,10 +228,27 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
 
     pad_rows = multigpu.max_local_rows(H, srows, world) if mode == "stripes" else H
     local = [torch.empty((pad_rows, W, 4), dtype=torch.uint8, device=dev) for _ in range(n_slots)]
+    # Striped frames, device output: every rank copies its rows straight to their global rows of RANK 0's frame (peer memory
+    # over NVLink, multigpu.PeerFrames) and the ranks' frame streams meet in a 4-byte all-reduce; --composite gather is the
+    # NCCL gather of the packed stripe buffers + an un-interleave pass on rank 0 it replaced.  Two frames per slot: a rank
+    # may start writing the slot's next frame while rank 0 still reads this one.
+    peer = mode == "stripes" and world > 1 and args.composite == "peer"
+    peer_frames = multigpu.PeerFrames(2 * n_slots, H * W * 4, rank, world, job.local_rank, barrier=job.barrier,
+                                      exchange=lambda blob: multigpu.broadcast_bytes(blob, 64 * 2 * n_slots, dev)) if peer else None
+    met = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(n_slots)] if peer else None
+    slot_uses = [0] * n_slots
     # rank 0: one contiguous [world, rows, W, 4] block per slot for the gathered frames / stripe buffers
-    blocks = [torch.empty((world, pad_rows, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None for _ in range(n_slots)]
+    blocks = [torch.empty((world, pad_rows, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0 and not peer) else None for _ in range(n_slots)]
     gathered = [list(b.unbind(0)) if b is not None else None for b in blocks]
-    full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (mode == "stripes" and rank == 0) else local[j] for j in range(n_slots)]
+    full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (mode == "stripes" and rank == 0 and not peer) else local[j] for j in range(n_slots)]
+
+    def striped_to_rank0(j):
+        """This rank's stripes of the current frame into rank 0's device frame (slot j); returns the frame's index in peer_frames."""
+        k = j + n_slots * (slot_uses[j] & 1)
+        slot_uses[j] += 1
+        r.on_render_striped_async(peer_frames.ptr(k), srows, rank, world)
+        multigpu.stream_barrier(met[j])
+        return k
     # host side of the e2e pass: per slot one [frames_per_step, H, W, 4] block every rank can write (see SharedHostFrames)
     frame_bytes = H * W * 4
     # the same name on every rank of this measurement (ranks may have run different numbers of solo measurements before it)
@@ -255,6 +279,8 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
             else:
                 if to_host:
                     r.on_render_striped_async(host.ptr(j), srows, rank, world)  # this rank's rows to their global rows of the shared frame
+                elif peer:
+                    striped_to_rank0(j)
                 else:
                     r.do_raytracing_striped_async(local[j].data_ptr(), srows, rank, world)
                     multigpu.gather_stripes(local[j], gathered[j], dst=0)
@@ -293,19 +319,22 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
             job.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(main)
-            with torch.cuda.stream(ext[0]):
-                ext[0].wait_event(e0)
+            j = r.next_frame_slot() if peer else 0  # the *_async call runs on the next frame slot's stream; the blocking calls on slot 0's
+            with torch.cuda.stream(ext[j]):
+                ext[j].wait_event(e0)
                 if mode == "single":
                     r.do_raytracing(local[0].data_ptr())
                 elif mode == "frames":
                     r.do_raytracing(local[0].data_ptr())
                     multigpu.gather_frames(local[0], gathered[0], dst=0)
+                elif peer:
+                    striped_to_rank0(j)
                 else:
                     r.do_raytracing_striped(local[0].data_ptr(), srows, rank, world)
                     multigpu.gather_stripes(local[0], gathered[0], dst=0)
                     if rank == 0:
                         multigpu.compose(full[0], gathered[0], H, srows, world)
-            main.wait_stream(ext[0])
+            main.wait_stream(ext[j])
             e1.record(main)
             e1.synchronize()
             total += job.max_over_ranks(e0.elapsed_time(e1))
@@ -352,7 +381,9 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
     # the caching allocator records an event on those streams when such a block is released
     job.barrier()
     host.close()
-    del local, gathered, blocks, full, flush, host
+    if peer_frames is not None:
+        peer_frames.close()
+    del local, gathered, blocks, full, flush, host, met, peer_frames
     import gc
     gc.collect()
     torch.cuda.synchronize()
@@ -387,7 +418,7 @@ def strong_scaling(job_all, args, math):
     return {
         "workload": CONFIGS[5]["workload"], "width": W, "height": H, "n_gpus": job_all.world, "scaling": "strong", "steps": steps * job_all.world, "warmup": warmup,
         "sharding": "one GPU, whole frame" if job_all.world == 1 else f"{plan['stripe_rows']}-row stripes interleaved over {job_all.world} ranks "
-                    "(gprt_dispatch_stripes), replicated scene and LBVH, NCCL gather of the RGBA8 rows to rank 0",
+                    "(gprt_dispatch_stripes), replicated scene and LBVH, " + STRIPE_COMPOSITE[args.composite],
         "frames_in_flight": plan["n_slots"], "ms_per_frame": round(mN["frame_ms"], 4), "value": round(mN["value"], 3), "unit": UNIT,
         "single_frame_ms": round(mN["single_frame_ms"], 4), "e2e_value": round(mN["e2e_value"], 3), "e2e_ms_per_frame": round(mN["e2e_ms_per_step"], 4),
         "rays_per_frame": mN["rays_per_step"],
@@ -643,6 +674,8 @@ def main():
                     help="N > 1: whole frames round-robin over the ranks, or row stripes of every frame; auto = frames up to 4 Mpixel, stripes above")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development runs of the large configs)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong_scaling leg (config 5 stripes) of the default config-2 run")
+    ap.add_argument("--composite", choices=("peer", "gather"), default="peer",
+                    help="striped frames, device output: rows written straight into rank 0's frame over NVLink (peer) or NCCL gather + un-interleave (gather)")
     ap.add_argument("--strong-steps", type=int, default=6, help="timed frames of the strong_scaling leg")
     ap.add_argument("--math", default=os.environ.get("GPRT_BENCH_MATH", "parity"), choices=["parity", "fma", "fast"])
     args = ap.parse_args()

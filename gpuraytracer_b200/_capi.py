@@ -52,6 +52,10 @@ class WaveStats(C.Structure):
                 ("node_visits", C.c_uint32), ("max_node_visits", C.c_uint32)]
 
 
+class IpcHandle(C.Structure):
+    _fields_ = [("bytes", C.c_ubyte * 64)]
+
+
 class Timing(C.Structure):
     _fields_ = [("dispatch_ms", C.c_float), ("build_accel_ms", C.c_float)]
 
@@ -124,6 +128,10 @@ def lib():
         "gprt_last_launch_count": (i32, [vp]),
         "gprt_alloc_host": (vp, [C.c_size_t]),
         "gprt_free_host": (None, [vp]),
+        "gprt_ipc_alloc": (i32, [i32, C.c_size_t, C.POINTER(vp), C.POINTER(IpcHandle)]),
+        "gprt_ipc_open": (i32, [i32, C.POINTER(IpcHandle), C.POINTER(vp)]),
+        "gprt_ipc_close": (i32, [i32, vp]),
+        "gprt_ipc_free": (i32, [i32, vp]),
         "gprt_error_string": (C.c_char_p, [i32]),
         "gprt_abi_version": (u32, []),
         "gprt_renderer_create": (i32, [C.POINTER(vp), i32, u32, u32, u32, i32, C.POINTER(Config)]),
@@ -193,6 +201,7 @@ EXPORTED_SYMBOLS = [
     "gprt_enable_peer_access", "gprt_multi_create", "gprt_multi_destroy", "gprt_multi_on_init", "gprt_multi_on_update", "gprt_multi_on_render_async",
     "gprt_multi_do_raytracing_async", "gprt_multi_wait_for_gpu", "gprt_multi_wait_for_frame_slot", "gprt_multi_set_frame_count", "gprt_multi_get_size", "gprt_multi_stripe_rows", "gprt_multi_context",
     "gprt_scene_create", "gprt_scene_destroy", "gprt_scene_update", "gprt_scene_get",
+    "gprt_ipc_alloc", "gprt_ipc_open", "gprt_ipc_close", "gprt_ipc_free",
 ]
 
 

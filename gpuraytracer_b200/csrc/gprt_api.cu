@@ -803,6 +803,46 @@ int gprt_enable_peer_access(gprt_ctx* c, int peer_device) {
 
 void* gprt_get_stream(gprt_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
+// ---- inter-process device frames (include/gprt.h) ----
+static_assert(sizeof(gprt_ipc_handle) == sizeof(cudaIpcMemHandle_t), "gprt_ipc_handle carries a cudaIpcMemHandle_t");
+static int ipc_status(cudaError_t e) {
+    if (e == cudaSuccess) return GPRT_OK;
+    cudaGetLastError();
+    return (e == cudaErrorNotSupported || e == cudaErrorPeerAccessUnsupported) ? GPRT_E_UNSUPPORTED : (e == cudaErrorMemoryAllocation ? GPRT_E_OUT_OF_MEMORY : GPRT_E_CUDA);
+}
+int gprt_ipc_alloc(int device_ordinal, size_t bytes, void** d_ptr, gprt_ipc_handle* handle) {
+    if (!d_ptr || !handle || bytes == 0) return GPRT_E_INVALID_ARG;
+    *d_ptr = nullptr;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
+    void* p = nullptr;
+    int rc = ipc_status(cudaMalloc(&p, bytes)); // its own allocation: the handle names the allocation, not an offset into a pool
+    if (rc != GPRT_OK) return rc;
+    cudaIpcMemHandle_t h;
+    rc = ipc_status(cudaIpcGetMemHandle(&h, p));
+    if (rc != GPRT_OK) { cudaFree(p); return rc; }
+    std::memcpy(handle->bytes, &h, sizeof h);
+    *d_ptr = p;
+    return GPRT_OK;
+}
+int gprt_ipc_open(int device_ordinal, const gprt_ipc_handle* handle, void** d_ptr) {
+    if (!d_ptr || !handle) return GPRT_E_INVALID_ARG;
+    *d_ptr = nullptr;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle->bytes, sizeof h);
+    return ipc_status(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+}
+int gprt_ipc_close(int device_ordinal, void* d_ptr) {
+    if (!d_ptr) return GPRT_OK;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
+    return ipc_status(cudaIpcCloseMemHandle(d_ptr));
+}
+int gprt_ipc_free(int device_ordinal, void* d_ptr) {
+    if (!d_ptr) return GPRT_OK;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess) { cudaGetLastError(); return GPRT_E_NO_DEVICE; }
+    return ipc_status(cudaFree(d_ptr));
+}
+
 int gprt_sync(gprt_ctx* c) {
     if (!c) return GPRT_E_INVALID_ARG;
     GPRT_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -143,3 +143,88 @@ class SharedHostFrames:
             except BufferError:
                 pass
             self._mm = None
+
+
+class _DevicePtr:
+    """A raw device pointer as a __cuda_array_interface__ object (what torch.as_tensor wraps without copying)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class PeerFrames:
+    """`n` DEVICE frames of `frame_bytes` on rank `owner`'s GPU that every rank of the box writes directly (one process
+    per GPU; C ABI: gprt_ipc_alloc / gprt_ipc_open).  With `ptr(k)` as the frame of on_render_striped_async every rank's
+    rows go over NVLink straight to their global rows of the owner's frame: the frame needs no gather and no un-interleave
+    pass, and the owner's GPU does nothing for it.  `exchange(bytes | None) -> bytes` hands the owner's handles to all
+    ranks (a broadcast); `barrier()` separates unmapping from freeing in close()."""
+
+    def __init__(self, n: int, frame_bytes: int, rank: int, world: int, device: int, exchange=None, barrier=None, owner: int = 0):
+        import ctypes as C
+
+        from ._capi import IpcHandle, check
+        self.n, self.frame_bytes, self.rank, self.world, self.device, self.owner = int(n), int(frame_bytes), int(rank), int(world), int(device), int(owner)
+        self._barrier = barrier or (lambda: None)
+        self._ptrs = []
+        L = lib()
+        blob = None
+        if rank == owner:
+            handles = []
+            for _ in range(self.n):
+                p, h = C.c_void_p(), IpcHandle()
+                check(L.gprt_ipc_alloc(self.device, self.frame_bytes, C.byref(p), C.byref(h)), "ipc_alloc")
+                self._ptrs.append(int(p.value))
+                handles.append(bytes(h.bytes))
+            blob = b"".join(handles)
+        if world > 1:
+            blob = exchange(blob)
+            if rank != owner:
+                for k in range(self.n):
+                    h = IpcHandle()
+                    C.memmove(h.bytes, blob[64 * k:64 * (k + 1)], 64)
+                    p = C.c_void_p()
+                    check(L.gprt_ipc_open(self.device, C.byref(h), C.byref(p)), "ipc_open")
+                    self._ptrs.append(int(p.value))
+
+    def ptr(self, k: int) -> int:
+        """Frame k as a device pointer valid in THIS process."""
+        return self._ptrs[k]
+
+    def tensor(self, k: int, shape):
+        """Frame k as a torch uint8 tensor (no copy); meant for the owner, which reads the finished frame."""
+        import torch
+        return torch.as_tensor(_DevicePtr(self._ptrs[k], self.frame_bytes), device=torch.device("cuda", self.device)).view(*shape)
+
+    def close(self):
+        L = lib()
+        if self.rank != self.owner:
+            for p in self._ptrs:
+                L.gprt_ipc_close(self.device, p)
+            self._ptrs = []
+        if self.world > 1:
+            self._barrier()
+        if self.rank == self.owner:
+            for p in self._ptrs:
+                L.gprt_ipc_free(self.device, p)
+            self._ptrs = []
+
+
+def broadcast_bytes(blob, nbytes: int, device, src: int = 0, group=None) -> bytes:
+    """`exchange` of PeerFrames over torch.distributed: `blob` (nbytes long) on rank `src`, None elsewhere."""
+    import torch
+    import torch.distributed as dist
+    if dist.get_backend(group) == "gloo":
+        device = "cpu"
+    t = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    if dist.get_rank(group) == src:
+        t.copy_(torch.frombuffer(bytearray(blob), dtype=torch.uint8))
+    dist.broadcast(t, src=src, group=group)
+    return bytes(t.cpu().numpy().tobytes())
+
+
+def stream_barrier(flag, group=None):
+    """All ranks' CURRENT streams meet: work enqueued after it on any rank runs after the work enqueued before it on every
+    rank (a 4-byte all-reduce; the call does not block the host).  After it the rows every rank copied into a PeerFrames
+    frame are in place."""
+    import torch.distributed as dist
+    dist.all_reduce(flag, group=group)

@@ -339,6 +339,19 @@ int gprt_last_launch_count(gprt_ctx* ctx);
 void* gprt_alloc_host(size_t bytes);
 void gprt_free_host(void* p);
 
+/* One process per GPU: a DEVICE frame of one rank as peer memory of the others, so that every rank's rows go straight to
+ * their place in rank 0's frame over NVLink (gprt_dispatch_stripes_host_async with the mapped pointer as h_frame_rgba8)
+ * and nothing is gathered or composed afterwards.  The owner allocates with gprt_ipc_alloc and hands the 64 opaque bytes
+ * to the other processes of the box by any means; they map it with gprt_ipc_open (peer access is enabled on first use)
+ * and unmap it with gprt_ipc_close before the owner calls gprt_ipc_free.  Ordering between the ranks is the caller's:
+ * the rows are in place once every rank's context stream has passed its copy (a barrier among the ranks' streams).
+ * GPRT_E_UNSUPPORTED where the driver has no inter-process memory handles (cudaIpcGetMemHandle). */
+typedef struct gprt_ipc_handle { unsigned char bytes[64]; } gprt_ipc_handle;
+int gprt_ipc_alloc(int device_ordinal, size_t bytes, void** d_ptr, gprt_ipc_handle* handle);
+int gprt_ipc_open(int device_ordinal, const gprt_ipc_handle* handle, void** d_ptr);
+int gprt_ipc_close(int device_ordinal, void* d_ptr);
+int gprt_ipc_free(int device_ordinal, void* d_ptr);
+
 const char* gprt_error_string(int status);
 uint32_t gprt_abi_version(void);
 

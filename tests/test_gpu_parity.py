@@ -546,6 +546,67 @@ def test_multi_device_renderer_equals_one_dispatch():
                 np.testing.assert_array_equal(frame.cpu().numpy(), want)
 
 
+_PEER_CHILD = r"""
+import sys
+sys.path.insert(0, {root!r})
+import ctypes as C
+from gpuraytracer_b200 import Renderer, default_config, _capi
+from gpuraytracer_b200._capi import IpcHandle, check, lib
+w, h, srows, rank, world, dev = (int(x) for x in sys.argv[1:7])
+hd = IpcHandle()
+C.memmove(hd.bytes, bytes.fromhex(sys.argv[7]), 64)
+p = C.c_void_p()
+check(lib().gprt_ipc_open(dev, C.byref(hd), C.byref(p)), "ipc_open")
+cfg = default_config()
+cfg.max_recursion_depth = cfg.metaballs_count = cfg.metaball_max_steps = cfg.sdf_max_steps = cfg.fractal_iterations = 0
+with Renderer(scene_id=0, width=w, height=h, device=dev, config=cfg) as r:
+    r.on_init()
+    r.on_update(0.8)
+    r.on_render_striped_async(p.value, srows, rank, world)
+    r.wait_for_gpu()
+check(lib().gprt_ipc_close(dev, p), "ipc_close")
+"""
+
+
+def test_stripes_of_other_processes_land_in_one_device_frame():
+    """gprt_ipc_*: one process per rank; the frame is device memory of the parent process, every other rank maps it and
+    its stripes go straight to their global rows (gprt_dispatch_stripes_host_async on the mapped pointer).  The assembled
+    frame is byte for byte the frame of a single gprt_dispatch."""
+    import ctypes as C
+    import subprocess
+    import sys
+
+    import torch
+    from gpuraytracer_b200 import multigpu
+    from gpuraytracer_b200._capi import IpcHandle, check, lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    n_dev = torch.cuda.device_count()
+    for (w, h, world) in ((320, 192, 2), (200, 150, 3)):
+        srows = multigpu.stripe_rows_for(h, world)
+        with Renderer(scene_id=0, width=w, height=h, device=0, config=make_cfg()) as r:
+            r.on_init()
+            r.on_update(0.8)
+            want, _ = r.on_render()
+            want = want.copy()
+            frames = multigpu.PeerFrames(1, w * h * 4, 0, 1, 0)          # the owner's side only: handles travel by argv here
+            hd = IpcHandle()
+            p = C.c_void_p()
+            check(lib().gprt_ipc_alloc(0, w * h * 4, C.byref(p), C.byref(hd)), "ipc_alloc")
+            try:
+                torch.cuda.synchronize()
+                for rank in range(1, world):
+                    out = subprocess.run([sys.executable, "-c", _PEER_CHILD.format(root=root), str(w), str(h), str(srows), str(rank), str(world),
+                                          str(rank % n_dev), bytes(hd.bytes).hex()], capture_output=True, text=True, timeout=300)
+                    assert out.returncode == 0, out.stderr[-2000:]
+                r.on_render_striped_async(p.value, srows, 0, world)
+                r.wait_for_gpu()
+                got = torch.as_tensor(multigpu._DevicePtr(p.value, w * h * 4), device="cuda:0").view(h, w, 4).cpu().numpy()
+                np.testing.assert_array_equal(got, want)
+            finally:
+                check(lib().gprt_ipc_free(0, p), "ipc_free")
+                frames.close()
+
+
 def test_headless_cli_over_several_devices_writes_the_same_frames(tmp_path):
     """gprt_render --devices: a C++ caller composes frames over several device contexts without Python; the PPM files are
     those of the single-device run byte for byte."""

@@ -81,7 +81,7 @@ def test_oracle_render_respects_fractal_iterations(oracle3):
 
 
 def _args(**kw):
-    d = dict(gpus=1, steps=2, warmup=3, config=2, frames_in_flight=0, multi_gpu="auto", math="parity")
+    d = dict(gpus=1, steps=2, warmup=3, config=2, frames_in_flight=0, multi_gpu="auto", math="parity", composite="peer")
     d.update(kw)
     return argparse.Namespace(**d)
 
