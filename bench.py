@@ -145,11 +145,16 @@ STRIPE_COMPOSITE = {"peer": "each rank's RGBA8 rows copied straight to their glo
                     "gather": "NCCL gather of the packed RGBA8 stripe buffers to rank 0 + an un-interleave pass there"}
 
 
+FRAME_COMPOSITE = {"peer": "every rank's final fold stores its RGBA8 frame straight into rank 0's device memory over NVLink (CUDA IPC peer memory), "
+                           "one 4-byte NCCL all-reduce per step as the barrier of the ranks' frame streams",
+                   "gather": "NCCL gather of the RGBA8 frames to rank 0"}
+
+
 def config_object(config_id, world, args, plan):
     """The `config` of the JSON line: a function of the command line only, so that the reference arm prints the same object."""
     mode, srows = plan["mode"], plan["stripe_rows"]
     par = {"single": "1 GPU",
-           "frames": f"{world} GPUs, whole frames round-robin (frame g on rank g % {world}), replicated scene, NCCL gather of the RGBA8 frames to rank 0; "
+           "frames": f"{world} GPUs, whole frames round-robin (frame g on rank g % {world}), replicated scene, " + FRAME_COMPOSITE[args.composite] + "; "
                      f"a step is {world} frames, one per rank",
            "stripes": f"{world} GPUs, {srows}-row stripes interleaved, replicated scene, " + STRIPE_COMPOSITE[args.composite]}[mode]
     return {"workload": CONFIGS[config_id]["workload"], "width": plan["width"], "height": plan["height"], "math_mode": args.math,
@@ -232,15 +237,24 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
     # over NVLink, multigpu.PeerFrames) and the ranks' frame streams meet in a 4-byte all-reduce; --composite gather is the
     # NCCL gather of the packed stripe buffers + an un-interleave pass on rank 0 it replaced.  Two frames per slot: a rank
     # may start writing the slot's next frame while rank 0 still reads this one.
-    peer = mode == "stripes" and world > 1 and args.composite == "peer"
-    peer_frames = multigpu.PeerFrames(2 * n_slots, H * W * 4, rank, world, job.local_rank, barrier=job.barrier,
-                                      exchange=lambda blob: multigpu.broadcast_bytes(blob, 64 * 2 * n_slots, dev)) if peer else None
+    peer = mode in ("stripes", "frames") and world > 1 and args.composite == "peer"
+    n_peer = 2 * n_slots * (world if mode == "frames" else 1)  # whole frames: one frame per rank and step, side by side in rank 0's memory
+    peer_frames = multigpu.PeerFrames(n_peer, H * W * 4, rank, world, job.local_rank, barrier=job.barrier,
+                                      exchange=lambda blob: multigpu.broadcast_bytes(blob, 64 * n_peer, dev)) if peer else None
     met = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(n_slots)] if peer else None
     slot_uses = [0] * n_slots
     # rank 0: one contiguous [world, rows, W, 4] block per slot for the gathered frames / stripe buffers
     blocks = [torch.empty((world, pad_rows, W, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0 and not peer) else None for _ in range(n_slots)]
     gathered = [list(b.unbind(0)) if b is not None else None for b in blocks]
     full = [torch.empty((H, W, 4), dtype=torch.uint8, device=dev) if (mode == "stripes" and rank == 0 and not peer) else local[j] for j in range(n_slots)]
+
+    def frame_to_rank0(j):
+        """This rank's whole frame of the step, written by the final fold itself into rank 0's memory (stores over NVLink)."""
+        k = (j + n_slots * (slot_uses[j] & 1)) * world + rank
+        slot_uses[j] += 1
+        r.do_raytracing_async(peer_frames.ptr(k))
+        multigpu.stream_barrier(met[j])
+        return k
 
     def striped_to_rank0(j):
         """This rank's stripes of the current frame into rank 0's device frame (slot j); returns the frame's index in peer_frames."""
@@ -273,6 +287,8 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
             elif mode == "frames":
                 if to_host:
                     r.on_render_async(host.ptr(j, rank * frame_bytes))  # frame i * N + rank, over this rank's own PCIe link
+                elif peer:
+                    frame_to_rank0(j)
                 else:
                     r.do_raytracing_async(local[j].data_ptr())
                     multigpu.gather_frames(local[j], gathered[j], dst=0)  # frame i * N + k from rank k
@@ -324,6 +340,8 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10):
                 ext[j].wait_event(e0)
                 if mode == "single":
                     r.do_raytracing(local[0].data_ptr())
+                elif mode == "frames" and peer:
+                    frame_to_rank0(j)
                 elif mode == "frames":
                     r.do_raytracing(local[0].data_ptr())
                     multigpu.gather_frames(local[0], gathered[0], dst=0)
