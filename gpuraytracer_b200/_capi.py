@@ -24,7 +24,8 @@ GPRT_HG_TRIANGLE, GPRT_HG_AABB_ANALYTIC, GPRT_HG_AABB_VOLUMETRIC, GPRT_HG_AABB_S
 
 GPRT_OK = 0
 GPRT_E_INVALID_ARG, GPRT_E_CUDA, GPRT_E_NO_DEVICE, GPRT_E_OUT_OF_MEMORY = -1, -2, -3, -4
-GPRT_E_NOT_BUILT, GPRT_E_QUEUE_OVERFLOW, GPRT_E_UNSUPPORTED, GPRT_E_ABI_MISMATCH = -5, -6, -7, -8
+GPRT_E_NOT_BUILT, GPRT_E_QUEUE_OVERFLOW, GPRT_E_UNSUPPORTED, GPRT_E_ABI_MISMATCH, GPRT_E_TOO_LARGE = -5, -6, -7, -8, -9
+GPRT_NOALLOC_MAX_PRIMS, GPRT_NOALLOC_SCRATCH_BYTES = 65536, 5 << 20
 
 
 class Config(C.Structure):
@@ -132,6 +133,8 @@ def lib():
         "gprt_ipc_open": (i32, [i32, C.POINTER(IpcHandle), C.POINTER(vp)]),
         "gprt_ipc_close": (i32, [i32, vp]),
         "gprt_ipc_free": (i32, [i32, vp]),
+        "gprt_lbvh_build_noalloc": (i32, [i32, vp, u32, vp, vp, vp, C.POINTER(C.c_int32), vp]),
+        "gprt_get_accel": (i32, [vp, u32, vp, vp, vp, C.POINTER(C.c_int32)]),
         "gprt_error_string": (C.c_char_p, [i32]),
         "gprt_abi_version": (u32, []),
         "gprt_renderer_create": (i32, [C.POINTER(vp), i32, u32, u32, u32, i32, C.POINTER(Config)]),
@@ -202,6 +205,7 @@ EXPORTED_SYMBOLS = [
     "gprt_multi_do_raytracing_async", "gprt_multi_wait_for_gpu", "gprt_multi_wait_for_frame_slot", "gprt_multi_set_frame_count", "gprt_multi_get_size", "gprt_multi_stripe_rows", "gprt_multi_context",
     "gprt_scene_create", "gprt_scene_destroy", "gprt_scene_update", "gprt_scene_get",
     "gprt_ipc_alloc", "gprt_ipc_open", "gprt_ipc_close", "gprt_ipc_free",
+    "gprt_lbvh_build_noalloc", "gprt_get_accel",
 ]
 
 

@@ -31,6 +31,7 @@ UNITS = [
     (os.path.join(CSRC, "lbvh.cu"), "lbvh.o", []),
     (os.path.join(CSRC, "fp32_probe.cu"), "fp32_probe.o", []),
     (os.path.join(CSRC, "transforms.cu"), "transforms.o", ["--fmad=false"]),
+    (os.path.join(CSRC, "noalloc.cu"), "noalloc.o", []),
     (os.path.join(CSRC, "gprt_api.cu"), "gprt_api.o", []),
     (os.path.join(CSRC, "gprt_common.cpp"), "gprt_common.o", []),
     (os.path.join(HOST, "scene.cpp"), "scene.o", []),

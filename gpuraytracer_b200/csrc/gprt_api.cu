@@ -595,6 +595,23 @@ int gprt_build_accel(gprt_ctx* c) {
     return GPRT_OK;
 }
 
+// Read-back of the context's binary LBVH (include/gprt.h): lets a test compare gprt_lbvh_build_noalloc with this builder.
+int gprt_get_accel(gprt_ctx* c, uint32_t n, void* h_nodes, uint32_t* h_sorted_prims, uint8_t* h_prim_tags, int32_t* root_ref) {
+    if (!c) return GPRT_E_INVALID_ARG;
+    if (!c->built) return GPRT_E_NOT_BUILT;
+    if (n != c->scene.n_prims) return GPRT_E_INVALID_ARG;
+    GPRT_CUDA(c, cudaSetDevice(c->device));
+    GPRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (h_nodes && n >= 2) GPRT_CUDA(c, cudaMemcpy(h_nodes, c->d_nodes, (size_t)(n - 1) * 4 * sizeof(float4), cudaMemcpyDeviceToHost));
+    if (h_sorted_prims && n >= 1) GPRT_CUDA(c, cudaMemcpy(h_sorted_prims, c->d_sorted, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    if (h_prim_tags && n >= 1) {
+        if (!c->d_prim_types) return GPRT_E_UNSUPPORTED;
+        GPRT_CUDA(c, cudaMemcpy(h_prim_tags, c->d_prim_types, (size_t)n, cudaMemcpyDeviceToHost));
+    }
+    if (root_ref) *root_ref = c->scene.root_ref;
+    return GPRT_OK;
+}
+
 int gprt_refit_accel(gprt_ctx* c, const gprt_aabb* aabbs, uint32_t n_aabbs) {
     if (!c || !aabbs) return GPRT_E_INVALID_ARG;
     if (!c->built) return GPRT_E_NOT_BUILT;

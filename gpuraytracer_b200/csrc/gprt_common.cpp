@@ -29,6 +29,7 @@ const char* gprt_error_string(int status) {
     case GPRT_E_QUEUE_OVERFLOW: return "candidate queue overflow (raise gprt_config.cand_per_ray or render in tiles)";
     case GPRT_E_UNSUPPORTED: return "unsupported configuration";
     case GPRT_E_ABI_MISMATCH: return "ABI version mismatch";
+    case GPRT_E_TOO_LARGE: return "size beyond the fixed scratch of this no-allocation entry point (GPRT_NOALLOC_MAX_PRIMS)";
     default: return "unknown gprt status";
     }
 }

@@ -191,7 +191,8 @@ typedef enum gprt_status {
     GPRT_E_NOT_BUILT       = -5, /* dispatch before gprt_build_accel                              */
     GPRT_E_QUEUE_OVERFLOW  = -6, /* raise gprt_config.cand_per_ray or render in tiles            */
     GPRT_E_UNSUPPORTED     = -7,
-    GPRT_E_ABI_MISMATCH    = -8
+    GPRT_E_ABI_MISMATCH    = -8,
+    GPRT_E_TOO_LARGE       = -9  /* beyond the fixed scratch of a no-allocation entry point (GPRT_NOALLOC_MAX_PRIMS) */
 } gprt_status;
 
 typedef struct gprt_ctx gprt_ctx;
@@ -351,6 +352,36 @@ int gprt_ipc_alloc(int device_ordinal, size_t bytes, void** d_ptr, gprt_ipc_hand
 int gprt_ipc_open(int device_ordinal, const gprt_ipc_handle* handle, void** d_ptr);
 int gprt_ipc_close(int device_ordinal, void* d_ptr);
 int gprt_ipc_free(int device_ordinal, void* d_ptr);
+
+/* ---- LBVH build that allocates nothing --------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same builder as gprt_build_accel
+ * (Morton codes, radix sort, Karras tree, box refit -- gprt::lbvh_build), over CALLER-owned device arrays, with its
+ * scratch (sort keys / values, radix histograms, child / parent links, refit flags, node boxes) in a fixed array in the
+ * library's device image instead of the context's cudaMalloc'd block.
+ *   d_aabbs         in:  n_aabbs x 6 floats (gprt_aabb), device memory
+ *   d_prim_tags     in:  optional (NULL: none) one byte per primitive, its low 4 bits stored in bits 27..30 of the
+ *                        primitive's leaf reference (the context passes the primitive type id here)
+ *   d_nodes         out: (n_aabbs - 1) x 64 bytes, the binary nodes (4 float4 each: two child boxes + two child refs)
+ *   d_sorted_prims  out: n_aabbs x uint32, the primitive index of every Morton-sorted leaf
+ *   root_ref        out (host): 0 = node 0 is the root, ~0 = a single leaf, INT32_MIN = empty
+ * Asynchronous on `cuda_stream` (cudaStream_t as void*, NULL = the default stream); the call makes `device_ordinal`
+ * current.  It calls no cudaMalloc / cudaFree or any allocating routine; the first call on a device looks the scratch
+ * array's address up once (cudaGetSymbolAddress), so a caller that captures graphs makes one call before capturing.
+ * Limits: n_aabbs <= GPRT_NOALLOC_MAX_PRIMS, else GPRT_E_TOO_LARGE and nothing is launched.  The scratch is
+ * GPRT_NOALLOC_SCRATCH_BYTES of device memory on EVERY GPU that loads the library, held until the process exits.
+ * ALL calls on a device share that one array and it keeps the previous call's contents (the builder clears the words that
+ * must start at zero itself): two calls that may overlap on the GPU -- different streams, or two host threads -- RACE;
+ * order them on one stream or with events. */
+#define GPRT_NOALLOC_MAX_PRIMS     65536u
+#define GPRT_NOALLOC_SCRATCH_BYTES (5u << 20)
+int gprt_lbvh_build_noalloc(int device_ordinal, const gprt_aabb* d_aabbs, uint32_t n_aabbs, const uint8_t* d_prim_tags,
+                            void* d_nodes, uint32_t* d_sorted_prims, int32_t* root_ref, void* cuda_stream);
+/* Reads back what gprt_build_accel / gprt_refit_accel built in `ctx`, for comparing the two builders (tests; blocking):
+ * the binary nodes (h_nodes: (n - 1) x 64 bytes), the sorted primitive indices (n x uint32), the tag bytes the context
+ * passed to its builder (n bytes) and the root reference; any of the pointers may be NULL.  `n` must be the context's AABB
+ * count.  Also no counterpart in the reference. */
+int gprt_get_accel(gprt_ctx* ctx, uint32_t n, void* h_nodes, uint32_t* h_sorted_prims, uint8_t* h_prim_tags, int32_t* root_ref);
 
 const char* gprt_error_string(int status);
 uint32_t gprt_abi_version(void);
