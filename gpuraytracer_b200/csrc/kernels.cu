@@ -332,9 +332,10 @@ __global__ void __launch_bounds__(kBlock) k_shade_spawn(const __grid_constant__ 
     WaveCtrl* next = &wb.ctrl[wave + 1];
     const int pq = wave & 1, nq = pq ^ 1;
     const uint32_t n_rays = (wave == 1) ? pp.n_pixels : min(ctrl->n_rays, pp.ray_capacity);
-    const uint32_t n_round = (n_rays + 31u) & ~31u;
-    const int lane = threadIdx.x & 31;
-    uint32_t cnt_radiance = 0, cnt_shadow = 0;
+    const uint32_t n_round = (n_rays + (uint32_t)kBlock - 1u) & ~((uint32_t)kBlock - 1u); // whole blocks: the loop has block-wide barriers
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ uint32_t s_total[2][kBlock / 32], s_base[2]; // double-buffered by trip parity: two barriers a trip are enough
+    uint32_t cnt_radiance = 0, cnt_shadow = 0, trip = 0;
     for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_round; r += gridDim.x * blockDim.x) {
         bool spawn_shadow = false, spawn_refl = false;
         V3 hit_pos = v3s(0.0f), sdir = v3s(0.0f), rdir = v3s(0.0f);
@@ -381,13 +382,24 @@ __global__ void __launch_bounds__(kBlock) k_shade_spawn(const __grid_constant__ 
                 }
             }
         }
-        // ballot/popc compaction into the next wave's queue
+        // ballot/popc compaction into the next wave's queue.  ONE reservation per block and trip: the counter is a single
+        // address, and one atomic per warp (a million of them for an 8K frame, serialised in L2 at ~2 ns each) was what this
+        // kernel spent most of its time on.
         const unsigned bs = __ballot_sync(kFull, spawn_shadow), br = __ballot_sync(kFull, spawn_refl);
         const uint32_t total = (uint32_t)(__popc(bs) + __popc(br));
+        const uint32_t pb = trip++ & 1u;
+        if (lane == 0) s_total[pb][warp] = total;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t sum = 0;
+#pragma unroll
+            for (int i = 0; i < kBlock / 32; i++) sum += s_total[pb][i];
+            s_base[pb] = sum ? atomicAdd(&next->n_rays, sum) : 0u;
+        }
+        __syncthreads();
         if (total) {
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&next->n_rays, total);
-            base = __shfl_sync(kFull, base, 0);
+            uint32_t base = s_base[pb];
+            for (int i = 0; i < warp; i++) base += s_total[pb][i];
             const unsigned lt = (1u << lane) - 1u;
             if (spawn_shadow) {
                 const uint32_t s = base + (uint32_t)__popc(bs & lt);
