@@ -312,11 +312,28 @@ __global__ void __launch_bounds__(kBlock) k_resolve(const __grid_constant__ Pass
     for (int type = 0; type < kNumTypes; type++) {
         if (!((type_mask >> type) & 1u)) continue;
         const uint32_t count = min(ctrl->cand_count[type], pp.cand_capacity);
-        for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < count; c += gridDim.x * blockDim.x) {
-            const float4 res = wb.cand_res[type][c];
-            if (res.w < 0.0f) continue;
-            const uint2 cand = wb.cand[type][c];
-            if (wb.hitkey[cand.x] == pack_key(res.w, cand.y)) wb.hit_n[cand.x] = res;
+        // a chain of three dependent loads per candidate and nothing to compute: kResolveIlp candidates per thread and trip,
+        // each stage of the chain issued for all of them before the next one is waited for
+        constexpr int kResolveIlp = 4;
+        const uint32_t stride = gridDim.x * blockDim.x;
+        for (uint32_t c0 = blockIdx.x * blockDim.x + threadIdx.x; c0 < count; c0 += kResolveIlp * stride) {
+            float4 res[kResolveIlp];
+            uint2 cand[kResolveIlp];
+            unsigned long long key[kResolveIlp];
+#pragma unroll
+            for (int i = 0; i < kResolveIlp; i++) {
+                const uint32_t c = c0 + (uint32_t)i * stride;
+                res[i] = c < count ? wb.cand_res[type][c] : make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+            }
+#pragma unroll
+            for (int i = 0; i < kResolveIlp; i++)
+                if (!(res[i].w < 0.0f)) cand[i] = wb.cand[type][c0 + (uint32_t)i * stride];
+#pragma unroll
+            for (int i = 0; i < kResolveIlp; i++)
+                if (!(res[i].w < 0.0f)) key[i] = wb.hitkey[cand[i].x];
+#pragma unroll
+            for (int i = 0; i < kResolveIlp; i++)
+                if (!(res[i].w < 0.0f) && key[i] == pack_key(res[i].w, cand[i].y)) wb.hit_n[cand[i].x] = res[i];
         }
     }
 }
@@ -641,7 +658,7 @@ int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuf
     return 1;
 }
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
-    k_resolve<<<sm_count() * 4, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
+    k_resolve<<<sm_count() * 8, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
     return 1;
 }
 
