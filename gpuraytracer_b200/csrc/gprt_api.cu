@@ -42,6 +42,9 @@ struct gprt_ctx {
     int last_cuda_error = 0;
     const KernelTable* kt = nullptr;       // traverse / resolve / shade_spawn / final: always the IEEE build
     const KernelTable* kt_isect = nullptr; // intersection (march) kernels: IEEE or fast-math build
+    cudaStream_t aux_stream = nullptr;     // GPRT_MATH_FMA: the IEEE march launch of a wave runs here beside the contracted one
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool serial_fma = false;               // GPRT_FMA_SERIAL=1: one after the other (measurement aid)
 
     // host copies of the static scene
     std::vector<gprt_aabb> h_aabbs;
@@ -429,9 +432,22 @@ int run_pass(gprt_ctx* c, const gprt_scene_cb* cb, uint32_t width, uint32_t heig
             // and reports the first sample over the threshold, so the same perturbation flips whole steps (config 4: 0.12 %,
             // over the 0.1 % bar).  The closed-form tests and the metaballs therefore always run the IEEE build.
             const uint32_t ieee_mask = (c->cfg.math_mode == GPRT_MATH_FMA) ? (c->type_mask & 0x7u) : 0u;
-            if (ieee_mask) launches += c->kt->intersect_all(c->scene, pp, c->wb, (int)wave, ieee_mask, (int)c->cfg.metaballs_count, c->stream);
-            if (c->type_mask & ~ieee_mask)
-                launches += c->kt_isect->intersect_all(c->scene, pp, c->wb, (int)wave, c->type_mask & ~ieee_mask, (int)c->cfg.metaballs_count, c->stream);
+            // The two launches run SIDE BY SIDE (the IEEE one on the context's second stream, one block per SM; the contracted
+            // one on the main stream, three per SM) and join before resolve: one after the other each would end in its own
+            // latency-bound tail, which cost more than the contraction saves.
+            const uint32_t rest = c->type_mask & ~ieee_mask;
+            const bool side_by_side = ieee_mask && rest && c->aux_stream && !c->serial_fma;
+            if (side_by_side) {
+                GPRT_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+                GPRT_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+                launches += c->kt->intersect_all(c->scene, pp, c->wb, (int)wave, ieee_mask, (int)c->cfg.metaballs_count, c->aux_stream, 1);
+                GPRT_CUDA(c, cudaEventRecord(c->ev_join, c->aux_stream));
+                launches += c->kt_isect->intersect_all(c->scene, pp, c->wb, (int)wave, rest, (int)c->cfg.metaballs_count, c->stream, 3);
+                GPRT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+            } else {
+                if (ieee_mask) launches += c->kt->intersect_all(c->scene, pp, c->wb, (int)wave, ieee_mask, (int)c->cfg.metaballs_count, c->stream, 0);
+                if (rest) launches += c->kt_isect->intersect_all(c->scene, pp, c->wb, (int)wave, rest, (int)c->cfg.metaballs_count, c->stream, 0);
+            }
         }
         if (c->type_mask) { ScopedInterval si(c, GPRT_K_RESOLVE); launches += c->kt->resolve(c->scene, pp, c->wb, (int)wave, c->type_mask, c->stream); }
         { ScopedInterval si(c, GPRT_K_SHADE_SPAWN); launches += c->kt->shade_spawn(c->scene, pp, c->wb, (int)wave, c->stream); }
@@ -501,6 +517,15 @@ int gprt_create(gprt_ctx** out, int device_ordinal, const gprt_config* cfg) {
     for (int i = 0; ok && i < kStagingSlots; i++) ok = cudaEventCreateWithFlags(&c->staging_done[i], cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaMallocHost((void**)&c->h_ctrl, sizeof(HostCtrlCopy) * kMaxBands) == cudaSuccess;
     if (!ok) { c->last_cuda_error = (int)cudaGetLastError(); gprt_destroy(c); return GPRT_E_CUDA; }
+    if (c0.math_mode == GPRT_MATH_FMA) {
+        c->serial_fma = getenv("GPRT_FMA_SERIAL") != nullptr;
+        if (cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+            c->aux_stream = nullptr; // falls back to one launch after the other
+        }
+    }
     std::memset(c->h_ctrl, 0, sizeof(HostCtrlCopy) * kMaxBands);
     *out = c;
     return GPRT_OK;
@@ -525,6 +550,9 @@ void gprt_destroy(gprt_ctx* c) {
     if (c->ev_stop) cudaEventDestroy(c->ev_stop);
     if (c->ev_build0) cudaEventDestroy(c->ev_build0);
     if (c->ev_build1) cudaEventDestroy(c->ev_build1);
+    if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }

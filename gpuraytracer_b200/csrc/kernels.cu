@@ -629,12 +629,11 @@ int launch_intersect(const SceneDev& sc, const PassParams& pp, const WaveBuffers
 }
 
 // the production path: every primitive type in one persistent launch per wave
-template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
-    static const int grid = [] {
-        const int full = persistent_grid(k_intersect_coop<NB, kRefillMin>);
-        const int lim = isect_blocks_limit(); // GPRT_ISECT_BLOCKS (tuning aid)
-        return (lim > 0 && lim * sm_count() < full) ? lim * sm_count() : full;
-    }();
+template <int NB> void launch_coop_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s, int blocks_per_sm) {
+    static const int full = persistent_grid(k_intersect_coop<NB, kRefillMin>);
+    int lim = isect_blocks_limit(); // GPRT_ISECT_BLOCKS (tuning aid)
+    if (blocks_per_sm > 0 && (lim <= 0 || blocks_per_sm < lim)) lim = blocks_per_sm;
+    const int grid = (lim > 0 && lim * sm_count() < full) ? lim * sm_count() : full;
     k_intersect_coop<NB, kRefillMin><<<grid, kCoopBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
 template <int NB> void launch_lane_t(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, cudaStream_t s) {
@@ -647,14 +646,14 @@ template <int NB> void launch_lane_t(const SceneDev& sc, const PassParams& pp, c
     }();
     k_intersect_lane<NB><<<sm_count() * per_sm, kCoopBlock, 0, s>>>(sc, pp, wb, wave, type_mask);
 }
-int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream) {
+int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, int metaballs, void* stream, int blocks_per_sm) {
     if (isect_variant() == 2) {
         if (metaballs == 5) launch_lane_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
         else launch_lane_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
         return 1;
     }
-    if (metaballs == 5) launch_coop_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
-    else launch_coop_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream);
+    if (metaballs == 5) launch_coop_t<5>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream, blocks_per_sm);
+    else launch_coop_t<3>(sc, pp, wb, wave, type_mask, (cudaStream_t)stream, blocks_per_sm);
     return 1;
 }
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {

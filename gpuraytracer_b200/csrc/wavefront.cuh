@@ -157,7 +157,8 @@ struct KernelTable {
     int (*traverse)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, void* stream);
     int (*intersect)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, int type_id, int metaballs, void* stream);
     // every type of `type_mask` in one persistent launch (the production path; `intersect` per type is the profiling path)
-    int (*intersect_all)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, uint32_t type_mask, int metaballs, void* stream);
+    // blocks_per_sm: 0 = a full resident wave of blocks; k = at most k per SM (two launches sharing the machine)
+    int (*intersect_all)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, uint32_t type_mask, int metaballs, void* stream, int blocks_per_sm);
     int (*resolve)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, uint32_t type_mask, void* stream);
     int (*shade_spawn)(const SceneDev&, const PassParams&, const WaveBuffers&, int wave, void* stream);
     int (*final_color)(const SceneDev&, const PassParams&, const WaveBuffers&, const OutputBuffers&, void* stream);
