@@ -33,7 +33,7 @@ def launches(src, dst):
     # one frame of the render loop: from a primary traverse to the final fold
     frame = []
     for name, ns in seq:
-        if name.startswith("k_traverse<1>"):
+        if name.startswith(("k_walk<1", "k_walk_deep<1", "k_traverse_brute<1")):  # the primary traversal opens a frame
             frame = []
         frame.append((name, round(ns / 1e3, 1)))
         if name.startswith("k_final_color") and len(frame) >= 13:
