@@ -309,8 +309,9 @@ __global__ void __launch_bounds__(kBlock) k_intersect(const __grid_constant__ Sc
 __global__ void __launch_bounds__(kBlock) k_resolve(const __grid_constant__ PassParams pp, const __grid_constant__ WaveBuffers wb, int wave,
                                                     uint32_t type_mask) {
     const WaveCtrl* ctrl = &wb.ctrl[wave];
-    for (int type = 0; type < kNumTypes; type++) {
-        if (!((type_mask >> type) & 1u)) continue;
+    { // one slice of the grid (blockIdx.y) per primitive type: the ten queues are resolved side by side
+        const int type = (int)blockIdx.y;
+        if (!((type_mask >> type) & 1u)) return;
         const uint32_t count = min(ctrl->cand_count[type], pp.cand_capacity);
         // a chain of three dependent loads per candidate and nothing to compute: kResolveIlp candidates per thread and trip,
         // each stage of the chain issued for all of them before the next one is waited for
@@ -657,7 +658,7 @@ int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuf
     return 1;
 }
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
-    k_resolve<<<sm_count() * 8, kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
+    k_resolve<<<dim3((unsigned)sm_count(), (unsigned)kNumTypes), kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
     return 1;
 }
 
