@@ -658,7 +658,7 @@ int launch_intersect_all(const SceneDev& sc, const PassParams& pp, const WaveBuf
     return 1;
 }
 int launch_resolve(const SceneDev&, const PassParams& pp, const WaveBuffers& wb, int wave, uint32_t type_mask, void* stream) {
-    k_resolve<<<dim3((unsigned)sm_count(), (unsigned)kNumTypes), kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
+    k_resolve<<<dim3((unsigned)sm_count() * 4u, (unsigned)kNumTypes), kBlock, 0, (cudaStream_t)stream>>>(pp, wb, wave, type_mask);
     return 1;
 }
 
