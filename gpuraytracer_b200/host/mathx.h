@@ -88,23 +88,57 @@ inline Mat4 mat_perspective_fov_lh(double fov_y, double aspect, double zn, doubl
     r.m[0][0] = w; r.m[1][1] = h; r.m[2][2] = q; r.m[2][3] = 1.0; r.m[3][2] = -q * zn;
     return r;
 }
+// Every row and column index below is a compile-time constant once the loops are unrolled (the pivot search keeps the
+// pivot's magnitude in a scalar and the row exchange tests `p == r` for each candidate row), so that the device build keeps
+// the 4 x 8 work array in registers and drops the columns nothing reads again; a run-time row index put it in local memory
+// (0.24 ms per frame for a million primitives, a fixed cost per GPU that one eighth of an 8K frame could not amortise).
+// The operations and their order are those of the textbook loop: same bits on the host and on the device.
+#if defined(__CUDACC__)
+#define GPRT_MX_UNROLL _Pragma("unroll")
+#else
+#define GPRT_MX_UNROLL
+#endif
 GPRT_MX Mat4 mat_inverse(const Mat4& a) { // XMMatrixInverse (general 4x4, Gauss-Jordan with partial pivoting)
     double w[4][8];
-    for (int i = 0; i < 4; i++)
+    GPRT_MX_UNROLL
+    for (int i = 0; i < 4; i++) {
+        GPRT_MX_UNROLL
         for (int j = 0; j < 4; j++) { w[i][j] = a.m[i][j]; w[i][j + 4] = (i == j) ? 1.0 : 0.0; }
+    }
+    GPRT_MX_UNROLL
     for (int c = 0; c < 4; c++) {
         int p = c;
-        for (int r = c + 1; r < 4; r++) if (fabs(w[r][c]) > fabs(w[p][c])) p = r;
-        if (p != c) for (int j = 0; j < 8; j++) { double t = w[c][j]; w[c][j] = w[p][j]; w[p][j] = t; }
-        const double d = w[c][c];
-        for (int j = 0; j < 8; j++) w[c][j] /= d;
-        for (int r = 0; r < 4; r++) if (r != c) {
-            const double f = w[r][c];
-            if (f != 0.0) for (int j = 0; j < 8; j++) w[r][j] -= f * w[c][j];
+        double best = fabs(w[c][c]);
+        GPRT_MX_UNROLL
+        for (int r = c + 1; r < 4; r++) {
+            const double v = fabs(w[r][c]);
+            if (v > best) { best = v; p = r; }
         }
+        GPRT_MX_UNROLL
+        for (int r = c + 1; r < 4; r++)
+            if (p == r) {
+                GPRT_MX_UNROLL
+                for (int j = 0; j < 8; j++) { const double t = w[c][j]; w[c][j] = w[r][j]; w[r][j] = t; }
+            }
+        const double d = w[c][c];
+        GPRT_MX_UNROLL
+        for (int j = 0; j < 8; j++) w[c][j] /= d;
+        GPRT_MX_UNROLL
+        for (int r = 0; r < 4; r++)
+            if (r != c) {
+                const double f = w[r][c];
+                if (f != 0.0) {
+                    GPRT_MX_UNROLL
+                    for (int j = 0; j < 8; j++) w[r][j] -= f * w[c][j];
+                }
+            }
     }
     Mat4 r;
-    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = w[i][j + 4];
+    GPRT_MX_UNROLL
+    for (int i = 0; i < 4; i++) {
+        GPRT_MX_UNROLL
+        for (int j = 0; j < 4; j++) r.m[i][j] = w[i][j + 4];
+    }
     return r;
 }
 GPRT_MX void mat_store(const Mat4& a, float out[16]) { // XMStoreFloat4x4 (row-major)
