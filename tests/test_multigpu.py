@@ -118,6 +118,51 @@ def test_frame_sharding_delivers_frames_in_order_over_gloo(tmp_path, world):
     np.testing.assert_array_equal(np.load(out), np.arange(4 * world))
 
 
+def _direct_worker(rank, world, port, height_crop, srows, out_path):
+    """The default composite of bench.py on CPU: rank 0 owns the frame and hands its handle to the others
+    (multigpu.broadcast_bytes -- here the name of a shared-memory file stands in for the 64-byte CUDA IPC handle),
+    every rank writes its stripes straight to their GLOBAL rows, and multigpu.stream_barrier (a 4-byte all-reduce) is the
+    point after which rank 0 may read the frame: no gather buffers, no un-interleave pass."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from gpuraytracer_b200 import multigpu as mg
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    golden = np.load(os.path.join(GOLDEN, "config1.npz"))["rgba8"][:height_crop]
+    h, w = golden.shape[:2]
+    handle = None
+    if rank == 0:
+        name = f"/dev/shm/gprt_test_{os.getpid()}_{port}".encode().ljust(64, b"\0")
+        np.lib.format.open_memmap(name.rstrip(b"\0").decode(), mode="w+", dtype=np.uint8, shape=(h, w, 4))[:] = 0
+        handle = name
+    handle = mg.broadcast_bytes(handle, 64, "cpu")
+    assert len(handle) == 64
+    path = handle.rstrip(b"\0").decode()
+    frame = np.load(path, mmap_mode="r+")
+    rows = mg.global_rows(h, srows, rank, world)
+    frame[rows] = golden[rows]  # stands in for gprt_dispatch_stripes_host_async on the mapped frame
+    frame.flush()
+    flag = torch.zeros(1, dtype=torch.int32)
+    mg.stream_barrier(flag)
+    if rank == 0:
+        np.save(out_path, np.array(frame))
+    dist.barrier()
+    if rank == 0:
+        os.unlink(path)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,height_crop,srows", [(2, 480, 8), (3, 100, 4), (2, 477, 5)])
+def test_ranks_write_their_rows_straight_into_one_frame_over_gloo(tmp_path, world, height_crop, srows):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "full.npy")
+    mp.spawn(_direct_worker, args=(world, _free_port(), height_crop, srows, out), nprocs=world, join=True)
+    golden = np.load(os.path.join(GOLDEN, "config1.npz"))["rgba8"][:height_crop]
+    np.testing.assert_array_equal(np.load(out), golden)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,srows,height", [(2, 8, 180), (4, 5, 180), (8, 3, 181), (3, 7, 90)])
 def test_striped_dispatch_equals_full_frame(world, srows, height):
