@@ -92,27 +92,6 @@ __device__ __forceinline__ bool fetch_lane(const SceneDev& sc, const WaveBuffers
     return true;
 }
 
-// The same for a march that k_march_tail continues: the "no hit" result is already in place.
-__device__ __forceinline__ bool fetch_lane_again(const SceneDev& sc, const WaveBuffers& wb, int pq, int type, uint32_t c, MarchLane& m) {
-    const uint2 cand = wb.cand[type][c];
-    m.c = c; m.r = cand.x;
-    const float4 rd = wb.ray_d[pq][m.r];
-    m.shadow = meta_shadow(__float_as_uint(rd.w)) != 0u;
-    if (m.shadow && __ldcg(&wb.hitkey[m.r]) != kKeyMiss) return false;
-    const float4 ro = wb.ray_o[pq][m.r];
-    const PrimRecord* pr = sc.prims + cand.y;
-    m.scale = pr->mat.step_scale;
-    const float* pf = sc.per_frame + 32 * (size_t)pr->instance_index;
-    const InstXform ix = inst_xform(sc, cand.y);
-    const V3 oo = xform_point_3x4(ix.w2o, ld3(ro)), dd = xform_vector_3x4(ix.w2o, ld3(rd));
-    m.o = mul_point_rowvec(oo, pf + 16);
-    m.d = mul_vector_rowvec(dd, pf + 16);
-    m.tcur = wb.ray_tcur[m.r];
-    m.t_stop = m.tcur;
-    m.active = true;
-    return true;
-}
-
 // ReportHit + the normal transform of the intersection shaders (src/Raytracing.hlsl:297-304)
 __device__ __forceinline__ void publish_lane_hit(const SceneDev& sc, const WaveBuffers& wb, int type, const MarchLane& m, float thit, V3 n_local) {
     if (thit >= 0.0f && thit <= m.tcur) {
