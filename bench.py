@@ -241,6 +241,14 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10, f
     n_peer = 2 * n_slots * (world if mode == "frames" else 1)  # whole frames: one frame per rank and step, side by side in rank 0's memory
     peer_frames = multigpu.PeerFrames(n_peer, H * W * 4, rank, world, job.local_rank, barrier=job.barrier,
                                       exchange=lambda blob: multigpu.broadcast_bytes(blob, 64 * n_peer, dev)) if peer else None
+    composite = ("peer" if peer else "gather") if world > 1 else "none (one GPU)"
+    if peer and job.max_over_ranks(1.0 if peer_frames.error else 0.0) > 0.0:
+        # some rank could not allocate or map the frames (no CUDA IPC in this environment, no peer access): every rank takes
+        # the NCCL gather instead, and the line says so
+        if rank == 0:
+            print(f"bench: peer-memory composite unavailable ({peer_frames.error or 'another rank failed'}); using the NCCL gather", file=sys.stderr)
+        peer_frames.close()
+        peer_frames, peer, composite = None, False, "gather (peer memory unavailable)"
     met = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(n_slots)] if peer else None
     slot_uses = [0] * n_slots
     # rank 0: one contiguous [world, rows, W, 4] block per slot for the gathered frames / stripe buffers
@@ -394,7 +402,7 @@ def measure(job, args, config_id, plan, steps, warmup, math, latency_steps=10, f
         "h2d_bytes_per_step": (136 + (0 if r.uses_device_transforms() else 128 * n_prims)) * frames_per_step,
         "d2h_bytes_per_step": W * H * 4 * frames_per_step,
         "device_transforms": r.uses_device_transforms(), "launches_per_step": launches_per_step,
-        "gpu_launches": launches_per_step * (2 * steps + lat_n), "n_prims": n_prims,
+        "gpu_launches": launches_per_step * (2 * steps + lat_n), "n_prims": n_prims, "composite": composite,
     }
     # free every tensor that was used on the frame streams BEFORE the contexts (and their streams) are destroyed:
     # the caching allocator records an event on those streams when such a block is released
@@ -440,7 +448,7 @@ def strong_scaling(job_all, args, math):
                     "(gprt_dispatch_stripes), replicated scene and LBVH, " + STRIPE_COMPOSITE[args.composite],
         "frames_in_flight": plan["n_slots"], "ms_per_frame": round(mN["frame_ms"], 4), "value": round(mN["value"], 3), "unit": UNIT,
         "single_frame_ms": round(mN["single_frame_ms"], 4), "e2e_value": round(mN["e2e_value"], 3), "e2e_ms_per_frame": round(mN["e2e_ms_per_step"], 4),
-        "rays_per_frame": mN["rays_per_step"],
+        "rays_per_frame": mN["rays_per_step"], "composite": mN["composite"],
         "n1": {"ms_per_frame": round(n1["frame_ms"], 4), "value": round(n1["value"], 3), "e2e_value": round(n1["e2e_value"], 3),
                "single_frame_ms": round(n1["single_frame_ms"], 4), "frames_in_flight": plan_for(5, 1, args)["n_slots"],
                "steps": steps, "how": "same run, rank 0 alone renders whole frames while the other ranks wait; `steps` frames here, N * `steps` "
@@ -502,6 +510,7 @@ def run_gpu(args):
                            + {"single": "", "frames": "; every rank copies its frame into the host block shared by all ranks (its own PCIe link)",
                               "stripes": "; every rank copies its rows to their global rows of the host frame shared by all ranks (its own PCIe link)"}[mode]},
             "gpu_launches": m["gpu_launches"],
+            "composite": m["composite"],  # how the device-resident frame(s) of a step reached rank 0 (what `config.parallelism` announces, or its fallback)
             "clocks": clocks,
         }
         if strong is not None:

@@ -159,32 +159,52 @@ class PeerFrames:
     pass, and the owner's GPU does nothing for it.  `exchange(bytes | None) -> bytes` hands the owner's handles to all
     ranks (a broadcast); `barrier()` separates unmapping from freeing in close()."""
 
-    def __init__(self, n: int, frame_bytes: int, rank: int, world: int, device: int, exchange=None, barrier=None, owner: int = 0):
+    def __init__(self, n: int, frame_bytes: int, rank: int, world: int, device: int, exchange=None, barrier=None, owner: int = 0, _lib=None):
+        """Collective over the `world` ranks and safe to fail in: a rank that cannot allocate or map never leaves the others
+        waiting in `exchange` -- it records the reason in `self.error` (None when all is well) and the ranks decide together
+        what to do (bench.py falls back to the NCCL gather when any rank reports an error; close() stays collective)."""
         import ctypes as C
 
-        from ._capi import IpcHandle, check
+        from ._capi import GprtError, IpcHandle, check
         self.n, self.frame_bytes, self.rank, self.world, self.device, self.owner = int(n), int(frame_bytes), int(rank), int(world), int(device), int(owner)
         self._barrier = barrier or (lambda: None)
         self._ptrs = []
-        L = lib()
+        self.error = None
+        self._L = L = _lib or lib()
         blob = None
         if rank == owner:
             handles = []
-            for _ in range(self.n):
-                p, h = C.c_void_p(), IpcHandle()
-                check(L.gprt_ipc_alloc(self.device, self.frame_bytes, C.byref(p), C.byref(h)), "ipc_alloc")
-                self._ptrs.append(int(p.value))
-                handles.append(bytes(h.bytes))
-            blob = b"".join(handles)
+            try:
+                for _ in range(self.n):
+                    p, h = C.c_void_p(), IpcHandle()
+                    check(L.gprt_ipc_alloc(self.device, self.frame_bytes, C.byref(p), C.byref(h)), "ipc_alloc")
+                    self._ptrs.append(int(p.value))
+                    handles.append(bytes(h.bytes))
+                blob = b"".join(handles)
+            except GprtError as e:
+                self.error = str(e)
+                for p in self._ptrs:
+                    L.gprt_ipc_free(self.device, p)
+                self._ptrs = []
+                blob = bytes(64 * self.n)  # all zeros: "no frames"
         if world > 1:
             blob = exchange(blob)
             if rank != owner:
-                for k in range(self.n):
-                    h = IpcHandle()
-                    C.memmove(h.bytes, blob[64 * k:64 * (k + 1)], 64)
-                    p = C.c_void_p()
-                    check(L.gprt_ipc_open(self.device, C.byref(h), C.byref(p)), "ipc_open")
-                    self._ptrs.append(int(p.value))
+                if not any(blob):
+                    self.error = f"rank {owner} could not allocate the frames"
+                else:
+                    try:
+                        for k in range(self.n):
+                            h = IpcHandle()
+                            C.memmove(h.bytes, blob[64 * k:64 * (k + 1)], 64)
+                            p = C.c_void_p()
+                            check(L.gprt_ipc_open(self.device, C.byref(h), C.byref(p)), "ipc_open")
+                            self._ptrs.append(int(p.value))
+                    except GprtError as e:
+                        self.error = str(e)
+                        for p in self._ptrs:
+                            L.gprt_ipc_close(self.device, p)
+                        self._ptrs = []
 
     def ptr(self, k: int) -> int:
         """Frame k as a device pointer valid in THIS process."""
@@ -196,7 +216,7 @@ class PeerFrames:
         return torch.as_tensor(_DevicePtr(self._ptrs[k], self.frame_bytes), device=torch.device("cuda", self.device)).view(*shape)
 
     def close(self):
-        L = lib()
+        L = self._L
         if self.rank != self.owner:
             for p in self._ptrs:
                 L.gprt_ipc_close(self.device, p)

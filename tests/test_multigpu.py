@@ -163,6 +163,73 @@ def test_ranks_write_their_rows_straight_into_one_frame_over_gloo(tmp_path, worl
     np.testing.assert_array_equal(np.load(out), golden)
 
 
+class _FakeIpcLib:
+    """Stands in for libgprt.so's gprt_ipc_* on CPU: hands out fake pointers; `fail` names the call that returns an error."""
+
+    def __init__(self, fail=None):
+        self.fail, self.live, self.next = fail, set(), 0x1000
+
+    def _new(self, p):
+        self.next += 0x1000
+        self.live.add(self.next)
+        p._obj.value = self.next
+
+    def gprt_ipc_alloc(self, dev, nbytes, p, h):
+        if self.fail == "alloc":
+            return -4
+        self._new(p)
+        h._obj.bytes[0] = 1 + len(self.live)
+        return 0
+
+    def gprt_ipc_open(self, dev, h, p):
+        if self.fail == "open":
+            return -7
+        self._new(p)
+        return 0
+
+    def gprt_ipc_close(self, dev, p):
+        self.live.discard(int(p))
+        return 0
+
+    gprt_ipc_free = gprt_ipc_close
+
+
+def _peer_failure_worker(rank, world, port, failing_rank, failing_call, out_dir):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from gpuraytracer_b200 import multigpu as mg
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    fake = _FakeIpcLib(fail=failing_call if rank == failing_rank else None)
+    frames = mg.PeerFrames(3, 1024, rank, world, 0, exchange=lambda blob: mg.broadcast_bytes(blob, 64 * 3, "cpu"), barrier=dist.barrier, _lib=fake)
+    bad = torch.tensor([1 if frames.error else 0])
+    dist.all_reduce(bad, op=dist.ReduceOp.MAX)  # what bench.py does: every rank learns whether any rank failed
+    frames.close()                                # collective, whatever happened
+    with open(os.path.join(out_dir, f"rank{rank}.txt"), "w") as f:
+        f.write(f"{int(bad.item())} {1 if frames.error else 0} {len(fake.live)}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("failing_rank,failing_call,expect_bad", [(None, None, 0), (0, "alloc", 1), (1, "open", 1)])
+def test_peer_frames_fail_collectively(tmp_path, failing_rank, failing_call, expect_bad):
+    """A rank that cannot allocate (owner) or map (any other rank) the peer frames must not leave the others hanging in
+    the handle exchange: all ranks finish construction, agree on the outcome, and close() frees / unmaps everything."""
+    import torch.multiprocessing as mp
+    world = 3
+    mp.spawn(_peer_failure_worker, args=(world, _free_port(), failing_rank, failing_call, str(tmp_path)), nprocs=world, join=True)
+    for rank in range(world):
+        bad, own_error, live = (int(x) for x in open(tmp_path / f"rank{rank}.txt").read().split())
+        assert bad == expect_bad
+        assert live == 0
+        if failing_call == "alloc":
+            assert own_error == 1          # the owner failed, the others saw an empty handle blob
+        elif failing_call == "open":
+            assert own_error == (1 if rank == failing_rank else 0)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,srows,height", [(2, 8, 180), (4, 5, 180), (8, 3, 181), (3, 7, 90)])
 def test_striped_dispatch_equals_full_frame(world, srows, height):
