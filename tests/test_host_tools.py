@@ -118,3 +118,62 @@ def test_reference_arm_ignores_omp_num_threads_and_never_maps_the_product_librar
     assert line["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
     assert line["config"]["multi_gpu"] == "frames" and line["config"]["width"] == 640
     assert maps == {"gprt": False, "scene": True, "oracle": True}
+
+
+_INVERSE_PIN = r"""
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include "gpuraytracer_b200/host/mathx.h"
+using gprt_host::Mat4;
+// the textbook loop mat_inverse restates with compile-time indices: Gauss-Jordan, partial pivoting by a run-time row index
+static Mat4 textbook(const Mat4& a) {
+    double w[4][8];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { w[i][j] = a.m[i][j]; w[i][j + 4] = (i == j) ? 1.0 : 0.0; }
+    for (int c = 0; c < 4; c++) {
+        int p = c;
+        for (int r = c + 1; r < 4; r++) if (std::fabs(w[r][c]) > std::fabs(w[p][c])) p = r;
+        if (p != c) for (int j = 0; j < 8; j++) { double t = w[c][j]; w[c][j] = w[p][j]; w[p][j] = t; }
+        const double d = w[c][c];
+        for (int j = 0; j < 8; j++) w[c][j] /= d;
+        for (int r = 0; r < 4; r++) if (r != c) { const double f = w[r][c]; if (f != 0.0) for (int j = 0; j < 8; j++) w[r][j] -= f * w[c][j]; }
+    }
+    Mat4 r;
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = w[i][j + 4];
+    return r;
+}
+int main() {
+    std::mt19937_64 rng(0);
+    std::uniform_real_distribution<double> u(-1.0, 1.0);
+    int bad = 0, n = 0;
+    for (int k = 0; k < 20000; k++) {
+        Mat4 m;
+        if (k % 2) { // the shape the renderer inverts: scale * rotationY * translation, translations up to +-2000
+            const double s = 0.2 + 1.5 * std::fabs(u(rng));
+            m = gprt_host::mat_mul(gprt_host::mat_mul(gprt_host::mat_scaling(s, s * (1.0 + 0.3 * u(rng)), s), gprt_host::mat_rotation_y(7.0 * u(rng))),
+                                   gprt_host::mat_translation(2000.0 * u(rng), 3.0 * u(rng), 2000.0 * u(rng)));
+        } else {
+            for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) m.m[i][j] = (k % 7 == 0 && i != j && (i + j) % 3 == 0) ? 0.0 : 10.0 * u(rng);
+        }
+        const Mat4 a = gprt_host::mat_inverse(m), b = textbook(m);
+        n++;
+        if (std::memcmp(a.m, b.m, sizeof a.m) != 0) bad++;
+    }
+    std::printf("%d %d\n", n, bad);
+    return bad != 0;
+}
+"""
+
+
+def test_matrix_inverse_with_static_indices_is_the_textbook_loop_bit_for_bit(tmp_path):
+    """host/mathx.h mat_inverse (XMMatrixInverse restated; also what the device-side transform update compiles) keeps every
+    index a compile-time constant; it must give the bits of the plain Gauss-Jordan loop with a run-time pivot row."""
+    src = tmp_path / "inv.cpp"
+    src.write_text(_INVERSE_PIN)
+    exe = tmp_path / "inv"
+    out = subprocess.run(["g++", "-O2", "-ffp-contract=off", "-I", ROOT, "-o", str(exe), str(src)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout
+    assert out.stdout.split() == ["20000", "0"]
